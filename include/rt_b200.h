@@ -1,0 +1,229 @@
+/* rt_b200.h — C ABI of the B200-native ray-tracing hot path.
+ *
+ * Drop-in boundary for the reference's CUDA entry point
+ *     void launch_compute_image_device(vec4* d_pixels, vec4* d_tmpPixels, vec4* d_image,
+ *          const int& width, const int& height, const Camera& camera, const vec4* d_lightsPos,
+ *          const vec4* d_lightsColor, const int& nLights, const vec4& background,
+ *          const vec4& ambience, const int& max_depth, const Data* data,
+ *          const BVH::BVHNodes_SoA* bvhNodes);            (reference mytracer_gpu.h:43-56)
+ * and its companion init_device() (mytracer_gpu.h:25), called only from
+ * Raytracer::compute_image_cuda() (mytracer.cpp:123-159).
+ *
+ * Plain C: pointers, sizes and PODs only; no C++/torch types.  Every function returns an
+ * rt_status (0 = OK) instead of the reference's print-and-continue CHECK macro
+ * (common/common.h:6-15); rt_last_error() gives the message of the calling thread's last
+ * failure.  One rt_scene may be used by one host thread at a time.
+ *
+ * Layout contracts
+ *   rt_vec4           == reference vec4: 4 doubles, 3 used (mydata.h uses vec4* arrays)
+ *   rt_data_soa       == struct Data            (mydata.h:28-72), field for field
+ *   rt_bvh_nodes_soa  == BVH::BVHNodes_SoA      (mybvh.h:49-55), field for field
+ * so a maintainer can pass reinterpret_cast'ed pointers to the reference's own structs
+ * (INTEGRATION.md).  Host, pinned or managed pointers are accepted for scene input.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_B200_ABI_VERSION 1
+
+typedef enum rt_status {
+  RT_OK = 0,
+  RT_ERR_INVALID_ARG = 1,   /* null pointer, negative count, bad enum */
+  RT_ERR_CUDA = 2,          /* a CUDA runtime call failed (message in rt_last_error) */
+  RT_ERR_NO_DEVICE = 3,     /* no CUDA device: there is NO CPU fallback */
+  RT_ERR_BAD_SCENE = 4,     /* BVH/Data arrays inconsistent (index out of range, cycle, ...) */
+  RT_ERR_LIMIT = 5,         /* BVH deeper than the traversal stack, too many lights, ... */
+  RT_ERR_OUT_OF_MEMORY = 6
+} rt_status;
+
+typedef struct rt_vec4 { double x, y, z, w; } rt_vec4;
+
+/* == struct Data (mydata.h:28-72).  Triangle rows (normals_, vertexIdx_, textureIdx_) must be
+ * in BVH order, i.e. after BVH::initSoA / rt_bvh_build_median permuted them. */
+typedef struct rt_data_soa {
+  int tMeshCount_, tVertexCount_, tVertexIdxCount_, tTextCoordCount_, tTextIdxCount_;
+  size_t tTexelCount_;
+  int *vertexMeshId_;          /* [tVertexCount_] */
+  rt_vec4 *vertexPos_;         /* [tVertexCount_] */
+  rt_vec4 *vertexNormals_;     /* [tVertexCount_] */
+  rt_vec4 *normals_;           /* [tVertexIdxCount_/3] face normals */
+  int *vertexIdx_;             /* [tVertexIdxCount_] global vertex ids, 3 per triangle */
+  int *textureIdx_;            /* [tTextIdxCount_]  global uv ids, 3 per triangle */
+  double *textureCoordinatesU_;/* [tTextCoordCount_] */
+  double *textureCoordinatesV_;
+  int *firstVertex_;     int *vertexCount_;        /* per mesh */
+  int *firstVertexIdx_;  int *vertexIdxCount_;
+  int *firstTextCoord_;  int *textCoordCount_;
+  int *firstTextIdx_;    int *textIdxCount_;
+  rt_vec4 *meshTexels_;        /* [tTexelCount_] all textures concatenated, row-major y*W+x */
+  int *meshTexWidth_;          /* -1 when the mesh has no texture */
+  int *meshTexHeight_;
+  size_t *firstMeshTex_;
+  int *meshDrawMode_;          /* 0 FLAT, 1 PHONG */
+  rt_vec4 *materialAmbient_;
+  rt_vec4 *materialDiffuse_;
+  rt_vec4 *materialSpecular_;
+  double *materialShininess_;
+  double *materialMirror_;
+  unsigned char *materialShadowable_; /* C++ bool[] */
+} rt_data_soa;
+
+/* == BVH::BVHNodes_SoA (mybvh.h:49-55).  Node 0 is the root; an interior node has
+ * triCount_ == 0 and children leftChildIdx_, leftChildIdx_+1.  The reference never records
+ * how many of the 2N-1 slots are used (mybvh.h:57), so consumers walk from the root. */
+typedef struct rt_bvh_nodes_soa {
+  rt_vec4 *bb_min_;
+  rt_vec4 *bb_max_;
+  int *leftChildIdx_;
+  int *firstTriIdx_;
+  int *triCount_;
+} rt_bvh_nodes_soa;
+
+typedef struct rt_material {
+  rt_vec4 ambient, diffuse, specular;
+  double shininess, mirror;
+  int shadowable;
+  int pad_;
+} rt_material;
+
+/* Analytic primitives of Raytracer::objects_ (mytracer.cpp:27), in list order.  They are not
+ * part of struct Data; the reference's CUDA path cannot render them, the CPU
+ * path can (myplane.cpp:22-49, Sphere from the course framework). */
+typedef enum rt_object_kind { RT_SPHERE = 0, RT_PLANE = 1 } rt_object_kind;
+typedef struct rt_object {
+  int kind;           /* rt_object_kind */
+  int pad_;
+  rt_vec4 center;
+  rt_vec4 normal;     /* planes */
+  double radius;      /* spheres */
+  rt_material material;
+} rt_object;
+
+/* Pinhole camera: primary_ray(x,y) = Ray(eye, lower_left + x*x_dir + y*y_dir - eye)
+ * (call sites mytracer_gpu.cu:141,208-209). */
+typedef struct rt_camera {
+  rt_vec4 eye, x_dir, y_dir, lower_left;
+  int width, height;
+} rt_camera;
+
+typedef struct rt_render_params {
+  rt_vec4 background;   /* Raytracer::background_ */
+  rt_vec4 ambience;     /* Raytracer::ambience_ */
+  int max_depth;        /* Raytracer::max_depth_: mirror bounces per primary ray */
+  int spp_grid;         /* s: s x s regular sub-pixel grid (1 = one centre ray), offsets as
+                           mytracer_gpu.cu:203-207 */
+  /* Image-tile sharding for multi-GPU: 8x4-pixel tiles are numbered row-major; this call
+   * renders tile t iff (t / tile_chunk) % tile_world == tile_rank.  1 GPU: world 1, rank 0. */
+  int tile_rank, tile_world, tile_chunk;
+  int flags;            /* RT_FLAG_* */
+} rt_render_params;
+
+#define RT_FLAG_EXACT_ONLY   1 /* validation: bypass the FP32 triangle filter (every test in FP64) */
+#define RT_FLAG_COUNTERS     2 /* run the instrumented kernel and fill rt_counters */
+#define RT_FLAG_NO_CLEAR     4 /* keep pixels of tiles owned by other ranks untouched */
+
+/* Output buffers; any pointer may be NULL.  All are W*H entries, index y*W + x
+ * (mytracer_gpu.cu:158). */
+typedef struct rt_frame_out {
+  uint8_t *rgba8;    /* 4 B/pixel: (int)(255*clamp(c,0,1)+0.5), alpha 255 */
+  rt_vec4 *pixels;   /* the reference's vec4 pixel buffer: rgb after min(c,1), w = 0 */
+  int32_t *hit_id;   /* primary (centre) ray: BVH-order triangle row, N + object index, -1 miss */
+  double *hit_t;     /* primary (centre) ray parameter, -1 on miss */
+} rt_frame_out;
+
+typedef struct rt_counters {
+  unsigned long long rays_primary, rays_shadow, rays_reflect;
+  unsigned long long box_tests;      /* child boxes tested (2 per visited interior node) */
+  unsigned long long tri_filter;     /* FP32 filter tests */
+  unsigned long long tri_exact;      /* FP64 confirmations */
+  unsigned long long object_tests;   /* analytic primitive tests */
+  unsigned long long shaded_hits;    /* lighting() evaluations */
+  unsigned long long texel_fetches;
+  unsigned long long nodes_visited;  /* interior node records loaded */
+} rt_counters;
+
+typedef struct rt_scene_info {
+  int num_triangles, num_meshes, num_objects;
+  int num_nodes_ref;       /* nodes reachable from the root in the reference layout */
+  int num_nodes_flat;      /* 64-byte two-child records */
+  int max_depth_bvh;
+  int max_leaf_size;
+  size_t blob_bytes;       /* flattened scene in HBM */
+  double flatten_ms, upload_ms;
+} rt_scene_info;
+
+typedef struct rt_scene rt_scene;
+
+/* ---- device ------------------------------------------------------------------------ */
+/* init_device() (mytracer_gpu.cu:32-39) with an explicit ordinal. */
+int rt_init_device(int device);
+const char *rt_last_error(void);
+int rt_abi_version(void);
+
+/* ---- scene: flatten + upload -------------------------------------------------------- */
+/* Walks the reference BVH from node 0, emits 64-byte float4 two-child node records with
+ * outward-rounded FP32 boxes, 48-byte FP32 triangle filter records, FP64 confirmation and
+ * shading records, texture objects; uploads one contiguous blob.  objects may be NULL. */
+int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
+                    int num_objects, rt_scene **out);
+int rt_scene_destroy(rt_scene *scene);
+int rt_scene_get_info(const rt_scene *scene, rt_scene_info *out);
+
+/* Multi-GPU replication: rank 0 exports the flattened blob (host copy), the caller broadcasts
+ * the bytes (NCCL), every other rank adopts them. */
+int rt_scene_blob_size(const rt_scene *scene, size_t *bytes);
+int rt_scene_blob_export(const rt_scene *scene, void *dst_host, size_t bytes);
+/* blob may be a host or a device pointer (is_device != 0: adopted with a D2D copy) */
+int rt_scene_create_from_blob(const void *blob, size_t bytes, int is_device, rt_scene **out);
+/* device address of the resident blob (for a device-side NCCL broadcast) */
+int rt_scene_blob_device_ptr(const rt_scene *scene, void **dptr, size_t *bytes);
+
+/* ---- render --------------------------------------------------------------------------- */
+/* Raytracer::compute_image_cuda() equivalent, HOST output buffers: uploads camera/lights,
+ * launches the kernel, copies the requested outputs back, synchronises. */
+int rt_render(rt_scene *scene, const rt_camera *camera, const rt_vec4 *lights_pos,
+              const rt_vec4 *lights_color, int num_lights, const rt_render_params *params,
+              const rt_frame_out *out_host);
+/* Same with DEVICE output buffers and device-resident light arrays (as the reference's
+ * d_lightsPos/d_lightsColor), asynchronous on `stream` (a cudaStream_t, 0 = legacy default). */
+int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_vec4 *d_lights_pos,
+                     const rt_vec4 *d_lights_color, int num_lights, const rt_render_params *params,
+                     const rt_frame_out *out_device, void *stream);
+int rt_get_counters(const rt_scene *scene, rt_counters *out);
+/* CUDA-event time of the last rt_render / rt_render_device kernel on this scene (ms);
+ * synchronises on the end event. */
+int rt_last_kernel_ms(const rt_scene *scene, float *ms);
+
+/* Exact-signature semantics of launch_compute_image_device (mytracer_gpu.cu:44-113): renders
+ * into d_pixels (device, vec4), runs the adaptive supersampling pass (subp 4, threshold 0.02,
+ * mytracer_gpu.cu:83-105,162-229) through d_tmpPixels, copies the result to h_image (host).
+ * data/bvh are flattened on first use and cached in *scene_cache (may start as NULL). */
+int rt_launch_compute_image(rt_vec4 *d_pixels, rt_vec4 *d_tmpPixels, rt_vec4 *h_image, int width,
+                            int height, const rt_camera *camera, const rt_vec4 *d_lightsPos,
+                            const rt_vec4 *d_lightsColor, int nLights, const rt_vec4 *background,
+                            const rt_vec4 *ambience, int max_depth, const rt_data_soa *data,
+                            const rt_bvh_nodes_soa *bvhNodes, rt_scene **scene_cache);
+
+/* ---- host-side scene preparation (callers of the path; same results as the reference) -- */
+/* BVH::initSoA (mybvh.cpp:375-539): median split on axis depth%3 (root depth 1), '<' partition,
+ * pairwise child allocation; permutes data->normals_/vertexIdx_/textureIdx_ rows in place.
+ * nodes: caller-allocated arrays of 2*N-1 entries.  nodes_used: out. */
+int rt_bvh_build_median(rt_data_soa *data, rt_bvh_nodes_soa *nodes, int *nodes_used);
+/* Mesh::compute_normals (mymesh.cpp:103-163) for one mesh: face normals and angle-weighted
+ * vertex normals.  pos/vnormals: nv vec4; idx: 3*nt local vertex ids; fnormals: nt vec4. */
+int rt_compute_normals(const rt_vec4 *pos, int nv, const int *idx, int nt, rt_vec4 *fnormals,
+                       rt_vec4 *vnormals);
+/* Pinhole camera from eye/center/up/fovy(deg) (build-defined; DESIGN.md "Conventions"). */
+int rt_camera_look_at(const double eye[3], const double center[3], const double up[3], double fovy_deg,
+                      int width, int height, rt_camera *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

@@ -1,0 +1,434 @@
+// rt_api.cu — implementation of the C ABI declared in include/rt_b200.h.
+//
+// Host plumbing that the reference spreads over Raytracer::compute_image_cuda /
+// prepareDeviceResources / copyLights / allocate (mytracer.cpp:68-159) and
+// launch_compute_image_device (mytracer_gpu.cu:44-113), rebuilt around one resident scene blob,
+// explicit streams and CUDA events, and status codes instead of print-and-continue.
+// There is no CPU fallback anywhere in this file.
+#include "../../include/rt_b200.h"
+#include "rt_flatten.h"
+#include "rt_frame.h"
+#include "rt_kernel.cuh"
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace rtb {
+static thread_local std::string g_err;
+void set_error(const std::string &m) { g_err = m; }
+} // namespace rtb
+
+using namespace rtb;
+
+#define RT_CUDA(call)                                                                              \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                               \
+      return (e_ == cudaErrorMemoryAllocation) ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA;               \
+    }                                                                                              \
+  } while (0)
+
+struct rt_scene {
+  int device = 0;
+  unsigned char *d_blob = nullptr;
+  size_t bytes = 0;
+  BlobHeader hdr;
+  SceneView view;
+  std::vector<cudaTextureObject_t> tex;
+  unsigned long long *d_tex = nullptr;
+  // per-frame device resources
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  unsigned long long *d_work = nullptr;
+  unsigned long long *d_counters = nullptr;
+  double *d_lights = nullptr; // pos[4*n] then col[4*n]
+  int lights_cap = 0;
+  // staging outputs for the host-buffer path
+  uint8_t *d_rgba8 = nullptr;
+  double *d_pixels = nullptr;
+  int32_t *d_ids = nullptr;
+  double *d_t = nullptr;
+  size_t cap_rgba8 = 0, cap_pixels = 0, cap_ids = 0, cap_t = 0;
+  int *d_list = nullptr; // supersampling pixel list
+  size_t cap_list = 0;
+  int grid_plain = 0, grid_count = 0;
+  rt_counters counters;
+  rt_scene_info info;
+  bool timed = false;
+};
+
+namespace {
+
+int ensure_device(std::string &err) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    err = std::string("no CUDA device available (") + cudaGetErrorString(e) +
+          "): this library has no CPU fallback";
+    return RT_ERR_NO_DEVICE;
+  }
+  return RT_OK;
+}
+
+template <typename T> int ensure_cap(T *&p, size_t &cap, size_t need_bytes) {
+  if (need_bytes <= cap) return RT_OK;
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+  RT_CUDA(cudaMalloc(&p, need_bytes));
+  RT_CUDA(cudaMemset(p, 0, need_bytes));
+  cap = need_bytes;
+  return RT_OK;
+}
+
+int adopt_blob(rt_scene *s) {
+  std::memset(&s->view, 0, sizeof(s->view));
+  const BlobHeader &h = s->hdr;
+  unsigned char *b = s->d_blob;
+  s->view.nodes = reinterpret_cast<const NodeRec *>(b + h.off_nodes);
+  s->view.filt = reinterpret_cast<const TriFilter *>(b + h.off_filter);
+  s->view.exact = reinterpret_cast<const TriExact *>(b + h.off_exact);
+  s->view.shade = reinterpret_cast<const TriShade *>(b + h.off_shade);
+  s->view.meshes = reinterpret_cast<const MeshRec *>(b + h.off_meshes);
+  s->view.objects = reinterpret_cast<const ObjectRec *>(b + h.off_objects);
+  s->view.texels = reinterpret_cast<const float *>(b + h.off_texels);
+  s->view.num_nodes = h.num_nodes; s->view.num_tris = h.num_tris;
+  s->view.num_meshes = h.num_meshes; s->view.num_objects = h.num_objects;
+  // texture objects over the blob's texel section ("textures go through texture objects")
+  std::vector<MeshRec> meshes(h.num_meshes);
+  if (h.num_meshes)
+    RT_CUDA(cudaMemcpy(meshes.data(), b + h.off_meshes, sizeof(MeshRec) * h.num_meshes, cudaMemcpyDeviceToHost));
+  s->tex.assign(h.num_meshes, 0);
+  for (int m = 0; m < h.num_meshes; ++m) {
+    if (meshes[m].tex_w == -1) continue;
+    cudaResourceDesc rd;
+    std::memset(&rd, 0, sizeof(rd));
+    rd.resType = cudaResourceTypeLinear;
+    rd.res.linear.devPtr = b + h.off_texels + meshes[m].tex_offset * 16;
+    rd.res.linear.desc = cudaCreateChannelDesc<float4>();
+    rd.res.linear.sizeInBytes = (size_t)meshes[m].tex_w * meshes[m].tex_h * 16;
+    cudaTextureDesc td;
+    std::memset(&td, 0, sizeof(td));
+    td.readMode = cudaReadModeElementType;
+    td.filterMode = cudaFilterModePoint;
+    td.addressMode[0] = cudaAddressModeClamp;
+    RT_CUDA(cudaCreateTextureObject(&s->tex[m], &rd, &td, nullptr));
+  }
+  if (h.num_meshes) {
+    RT_CUDA(cudaMalloc(&s->d_tex, sizeof(unsigned long long) * h.num_meshes));
+    RT_CUDA(cudaMemcpy(s->d_tex, s->tex.data(), sizeof(unsigned long long) * h.num_meshes, cudaMemcpyHostToDevice));
+  }
+  s->view.tex_objs = s->d_tex;
+  RT_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  RT_CUDA(cudaEventCreate(&s->ev0));
+  RT_CUDA(cudaEventCreate(&s->ev1));
+  RT_CUDA(cudaMalloc(&s->d_work, sizeof(unsigned long long)));
+  RT_CUDA(cudaMalloc(&s->d_counters, sizeof(unsigned long long) * C_COUNT));
+  // persistent grid: SM count x resident CTAs of each kernel variant
+  cudaDeviceProp prop;
+  RT_CUDA(cudaGetDeviceProperties(&prop, s->device));
+  int occ0 = 0, occ1 = 0;
+  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, render_kernel<false>, kBlockThreads, 0));
+  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, render_kernel<true>, kBlockThreads, 0));
+  s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
+  s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
+  std::memset(&s->info, 0, sizeof(s->info));
+  s->info.num_triangles = h.num_tris; s->info.num_meshes = h.num_meshes; s->info.num_objects = h.num_objects;
+  s->info.num_nodes_ref = h.num_nodes_ref; s->info.num_nodes_flat = h.num_nodes;
+  s->info.max_depth_bvh = h.max_depth; s->info.max_leaf_size = h.max_leaf; s->info.blob_bytes = s->bytes;
+  std::memset(&s->counters, 0, sizeof(s->counters));
+  return RT_OK;
+}
+
+int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const double *d_lcol, const FrameOut &out,
+           const int *d_list, int list_count, cudaStream_t st, const int *d_list_count = nullptr) {
+  KernelArgs a;
+  a.sv = s->view; a.fp = fp;
+  a.light_pos = d_lpos; a.light_col = d_lcol;
+  a.out = out;
+  a.pixel_list = d_list; a.list_count = list_count;
+  a.list_count_ptr = d_list_count;
+  a.work_counter = s->d_work;
+  a.counters = s->d_counters;
+  const bool count = (fp.flags & RT_FLAG_COUNTERS) != 0;
+  RT_CUDA(cudaMemsetAsync(s->d_work, 0, sizeof(unsigned long long), st));
+  if (count) RT_CUDA(cudaMemsetAsync(s->d_counters, 0, sizeof(unsigned long long) * C_COUNT, st));
+  RT_CUDA(cudaEventRecord(s->ev0, st));
+  if (count) render_kernel<true><<<s->grid_count, kBlockThreads, 0, st>>>(a);
+  else render_kernel<false><<<s->grid_plain, kBlockThreads, 0, st>>>(a);
+  RT_CUDA(cudaGetLastError());
+  RT_CUDA(cudaEventRecord(s->ev1, st));
+  s->timed = true;
+  return RT_OK;
+}
+
+int fetch_counters(rt_scene *s, cudaStream_t st) {
+  unsigned long long h[C_COUNT];
+  RT_CUDA(cudaMemcpyAsync(h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaStreamSynchronize(st));
+  rt_counters &c = s->counters;
+  c.rays_primary = h[C_RAY_PRIMARY]; c.rays_shadow = h[C_RAY_SHADOW]; c.rays_reflect = h[C_RAY_REFLECT];
+  c.box_tests = h[C_BOX]; c.tri_filter = h[C_TRI_FILTER]; c.tri_exact = h[C_TRI_EXACT];
+  c.object_tests = h[C_OBJECT]; c.shaded_hits = h[C_SHADED]; c.texel_fetches = h[C_TEXEL];
+  c.nodes_visited = h[C_NODES];
+  return RT_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int rt_abi_version(void) { return RT_B200_ABI_VERSION; }
+const char *rt_last_error(void) { return g_err.c_str(); }
+
+int rt_init_device(int device) {
+  std::string err;
+  int st = ensure_device(err);
+  if (st != RT_OK) { set_error(err); return st; }
+  RT_CUDA(cudaSetDevice(device));
+  RT_CUDA(cudaFree(nullptr));
+  return RT_OK;
+}
+
+int rt_scene_create_from_blob(const void *blob, size_t bytes, int is_device, rt_scene **out) {
+  if (!blob || !out) { set_error("rt_scene_create_from_blob: null argument"); return RT_ERR_INVALID_ARG; }
+  std::string err;
+  int st = ensure_device(err);
+  if (st != RT_OK) { set_error(err); return st; }
+  const auto t0 = std::chrono::steady_clock::now();
+  BlobHeader h;
+  if (bytes < sizeof(h)) { set_error("blob: too small"); return RT_ERR_INVALID_ARG; }
+  if (is_device) RT_CUDA(cudaMemcpy(&h, blob, sizeof(h), cudaMemcpyDeviceToHost));
+  else std::memcpy(&h, blob, sizeof(h));
+  {
+    // validate the section table (header only; the payload was produced by flatten_scene)
+    std::vector<unsigned char> hb(sizeof(h));
+    std::memcpy(hb.data(), &h, sizeof(h));
+    if (h.magic != kBlobMagic || h.version != kBlobVersion || h.total_bytes != bytes) {
+      set_error("blob: bad magic/version/size");
+      return RT_ERR_BAD_SCENE;
+    }
+  }
+  rt_scene *s = new rt_scene();
+  RT_CUDA(cudaGetDevice(&s->device));
+  s->bytes = bytes;
+  s->hdr = h;
+  cudaError_t e = cudaMalloc(&s->d_blob, bytes);
+  if (e != cudaSuccess) { delete s; set_error("cudaMalloc(blob) failed"); return RT_ERR_OUT_OF_MEMORY; }
+  e = cudaMemcpy(s->d_blob, blob, bytes, is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { cudaFree(s->d_blob); delete s; set_error("blob upload failed"); return RT_ERR_CUDA; }
+  st = adopt_blob(s);
+  if (st != RT_OK) { rt_scene_destroy(s); return st; }
+  s->info.upload_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  *out = s;
+  return RT_OK;
+}
+
+int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
+                    int num_objects, rt_scene **out) {
+  if (!out) { set_error("rt_scene_create: null out"); return RT_ERR_INVALID_ARG; }
+  std::string err;
+  int st = ensure_device(err);
+  if (st != RT_OK) { set_error(err); return st; }
+  const auto t0 = std::chrono::steady_clock::now();
+  std::vector<unsigned char> blob;
+  st = flatten_scene(data, bvh, objects, num_objects, blob, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  const double flat_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  st = rt_scene_create_from_blob(blob.data(), blob.size(), 0, out);
+  if (st == RT_OK) (*out)->info.flatten_ms = flat_ms;
+  return st;
+}
+
+int rt_scene_destroy(rt_scene *s) {
+  if (!s) return RT_OK;
+  for (cudaTextureObject_t t : s->tex) if (t) cudaDestroyTextureObject(t);
+  auto F = [](void *p) { if (p) cudaFree(p); };
+  F(s->d_blob); F(s->d_tex); F(s->d_work); F(s->d_counters); F(s->d_lights);
+  F(s->d_rgba8); F(s->d_pixels); F(s->d_ids); F(s->d_t); F(s->d_list);
+  if (s->ev0) cudaEventDestroy(s->ev0);
+  if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+  return RT_OK;
+}
+
+int rt_scene_get_info(const rt_scene *s, rt_scene_info *out) {
+  if (!s || !out) { set_error("rt_scene_get_info: null argument"); return RT_ERR_INVALID_ARG; }
+  *out = s->info;
+  return RT_OK;
+}
+
+int rt_scene_blob_size(const rt_scene *s, size_t *bytes) {
+  if (!s || !bytes) { set_error("rt_scene_blob_size: null argument"); return RT_ERR_INVALID_ARG; }
+  *bytes = s->bytes;
+  return RT_OK;
+}
+
+int rt_scene_blob_export(const rt_scene *s, void *dst, size_t bytes) {
+  if (!s || !dst || bytes < s->bytes) { set_error("rt_scene_blob_export: bad argument"); return RT_ERR_INVALID_ARG; }
+  RT_CUDA(cudaMemcpy(dst, s->d_blob, s->bytes, cudaMemcpyDeviceToHost));
+  return RT_OK;
+}
+
+int rt_scene_blob_device_ptr(const rt_scene *s, void **dptr, size_t *bytes) {
+  if (!s || !dptr || !bytes) { set_error("rt_scene_blob_device_ptr: null argument"); return RT_ERR_INVALID_ARG; }
+  *dptr = s->d_blob;
+  *bytes = s->bytes;
+  return RT_OK;
+}
+
+int rt_render_device(rt_scene *s, const rt_camera *camera, const rt_vec4 *d_lights_pos,
+                     const rt_vec4 *d_lights_color, int num_lights, const rt_render_params *params,
+                     const rt_frame_out *out, void *stream) {
+  if (!s) { set_error("rt_render_device: null scene"); return RT_ERR_INVALID_ARG; }
+  FrameParams fp;
+  std::string err;
+  int st = make_frame_params(camera, num_lights, params, out, fp, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  if (num_lights > 0 && (!d_lights_pos || !d_lights_color)) { set_error("rt_render_device: null lights"); return RT_ERR_INVALID_ARG; }
+  FrameOut fo;
+  fo.rgba8 = out->rgba8; fo.pixels = reinterpret_cast<double *>(out->pixels);
+  fo.hit_id = out->hit_id; fo.hit_t = out->hit_t;
+  cudaStream_t stx = static_cast<cudaStream_t>(stream);
+  st = launch(s, fp, reinterpret_cast<const double *>(d_lights_pos), reinterpret_cast<const double *>(d_lights_color),
+              fo, nullptr, 0, stx);
+  if (st != RT_OK) return st;
+  if (fp.flags & RT_FLAG_COUNTERS) return fetch_counters(s, stx);
+  return RT_OK;
+}
+
+int rt_render(rt_scene *s, const rt_camera *camera, const rt_vec4 *lights_pos, const rt_vec4 *lights_color,
+              int num_lights, const rt_render_params *params, const rt_frame_out *out) {
+  if (!s) { set_error("rt_render: null scene"); return RT_ERR_INVALID_ARG; }
+  FrameParams fp;
+  std::string err;
+  int st = make_frame_params(camera, num_lights, params, out, fp, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  if (num_lights > 0 && (!lights_pos || !lights_color)) { set_error("rt_render: null lights"); return RT_ERR_INVALID_ARG; }
+  const size_t npx = (size_t)camera->width * camera->height;
+  cudaStream_t stx = s->stream;
+  // lights: host -> device every frame (copyLights, mytracer.cpp:105-118)
+  if (num_lights > s->lights_cap) {
+    if (s->d_lights) cudaFree(s->d_lights);
+    s->d_lights = nullptr;
+    RT_CUDA(cudaMalloc(&s->d_lights, sizeof(double) * 8 * num_lights));
+    s->lights_cap = num_lights;
+  }
+  if (num_lights > 0) {
+    RT_CUDA(cudaMemcpyAsync(s->d_lights, lights_pos, sizeof(double) * 4 * num_lights, cudaMemcpyHostToDevice, stx));
+    RT_CUDA(cudaMemcpyAsync(s->d_lights + 4 * (size_t)s->lights_cap, lights_color, sizeof(double) * 4 * num_lights,
+                            cudaMemcpyHostToDevice, stx));
+  }
+  FrameOut fo;
+  std::memset(&fo, 0, sizeof(fo));
+  const bool partial = fp.tile_world > 1 && !(fp.flags & RT_FLAG_NO_CLEAR);
+  if (out->rgba8) {
+    st = ensure_cap(s->d_rgba8, s->cap_rgba8, npx * 4); if (st != RT_OK) return st;
+    fo.rgba8 = s->d_rgba8;
+    if (partial) RT_CUDA(cudaMemsetAsync(s->d_rgba8, 0, npx * 4, stx));
+  }
+  if (out->pixels) {
+    st = ensure_cap(s->d_pixels, s->cap_pixels, npx * 32); if (st != RT_OK) return st;
+    fo.pixels = s->d_pixels;
+    if (partial) RT_CUDA(cudaMemsetAsync(s->d_pixels, 0, npx * 32, stx));
+  }
+  if (out->hit_id) {
+    st = ensure_cap(s->d_ids, s->cap_ids, npx * 4); if (st != RT_OK) return st;
+    fo.hit_id = s->d_ids;
+    if (partial) RT_CUDA(cudaMemsetAsync(s->d_ids, 0xff, npx * 4, stx));
+  }
+  if (out->hit_t) {
+    st = ensure_cap(s->d_t, s->cap_t, npx * 8); if (st != RT_OK) return st;
+    fo.hit_t = s->d_t;
+    if (partial) RT_CUDA(cudaMemsetAsync(s->d_t, 0, npx * 8, stx));
+  }
+  st = launch(s, fp, s->d_lights, s->d_lights + 4 * (size_t)s->lights_cap, fo, nullptr, 0, stx);
+  if (st != RT_OK) return st;
+  if (out->rgba8) RT_CUDA(cudaMemcpyAsync(out->rgba8, s->d_rgba8, npx * 4, cudaMemcpyDeviceToHost, stx));
+  if (out->pixels) RT_CUDA(cudaMemcpyAsync(out->pixels, s->d_pixels, npx * 32, cudaMemcpyDeviceToHost, stx));
+  if (out->hit_id) RT_CUDA(cudaMemcpyAsync(out->hit_id, s->d_ids, npx * 4, cudaMemcpyDeviceToHost, stx));
+  if (out->hit_t) RT_CUDA(cudaMemcpyAsync(out->hit_t, s->d_t, npx * 8, cudaMemcpyDeviceToHost, stx));
+  if (fp.flags & RT_FLAG_COUNTERS) {
+    st = fetch_counters(s, stx);
+    if (st != RT_OK) return st;
+  }
+  RT_CUDA(cudaStreamSynchronize(stx));
+  return RT_OK;
+}
+
+int rt_get_counters(const rt_scene *s, rt_counters *out) {
+  if (!s || !out) { set_error("rt_get_counters: null argument"); return RT_ERR_INVALID_ARG; }
+  *out = s->counters;
+  return RT_OK;
+}
+
+int rt_last_kernel_ms(const rt_scene *s, float *ms) {
+  if (!s || !ms) { set_error("rt_last_kernel_ms: null argument"); return RT_ERR_INVALID_ARG; }
+  if (!s->timed) { set_error("rt_last_kernel_ms: nothing rendered yet"); return RT_ERR_INVALID_ARG; }
+  RT_CUDA(cudaEventSynchronize(s->ev1));
+  RT_CUDA(cudaEventElapsedTime(ms, s->ev0, s->ev1));
+  return RT_OK;
+}
+
+int rt_launch_compute_image(rt_vec4 *d_pixels, rt_vec4 *d_tmpPixels, rt_vec4 *h_image, int width, int height,
+                            const rt_camera *camera, const rt_vec4 *d_lightsPos, const rt_vec4 *d_lightsColor,
+                            int nLights, const rt_vec4 *background, const rt_vec4 *ambience, int max_depth,
+                            const rt_data_soa *data, const rt_bvh_nodes_soa *bvhNodes, rt_scene **scene_cache) {
+  if (!d_pixels || !d_tmpPixels || !camera || !background || !ambience || !scene_cache) {
+    set_error("rt_launch_compute_image: null argument");
+    return RT_ERR_INVALID_ARG;
+  }
+  if (width != camera->width || height != camera->height) {
+    set_error("rt_launch_compute_image: width/height differ from the camera's");
+    return RT_ERR_INVALID_ARG;
+  }
+  int st;
+  if (!*scene_cache) {
+    st = rt_scene_create(data, bvhNodes, nullptr, 0, scene_cache);
+    if (st != RT_OK) return st;
+  }
+  rt_scene *s = *scene_cache;
+  cudaStream_t stx = s->stream;
+  const size_t npx = (size_t)width * height;
+  rt_render_params p;
+  std::memset(&p, 0, sizeof(p));
+  p.background = *background; p.ambience = *ambience; p.max_depth = max_depth;
+  p.spp_grid = 1; p.tile_world = 1; p.tile_chunk = 1;
+  rt_frame_out fo;
+  std::memset(&fo, 0, sizeof(fo));
+  fo.pixels = d_pixels;
+  // pass 1: compute_image_device (mytracer_gpu.cu:66-77)
+  st = rt_render_device(s, camera, d_lightsPos, d_lightsColor, nLights, &p, &fo, stx);
+  if (st != RT_OK) return st;
+  // pass 2: adaptive supersampling, subp = 4, threshold = 0.02 (mytracer_gpu.cu:83-105)
+  RT_CUDA(cudaMemcpyAsync(d_tmpPixels, d_pixels, npx * sizeof(rt_vec4), cudaMemcpyDeviceToDevice, stx));
+  st = ensure_cap(s->d_list, s->cap_list, (npx + 1) * sizeof(int));
+  if (st != RT_OK) return st;
+  int *d_count = s->d_list + npx;
+  RT_CUDA(cudaMemsetAsync(d_count, 0, sizeof(int), stx));
+  const dim3 blk(32, 8), grd((width + 31) / 32, (height + 7) / 8);
+  flag_contrast_kernel<<<grd, blk, 0, stx>>>(reinterpret_cast<const double *>(d_tmpPixels), width, height, 0.02,
+                                              s->d_list, d_count);
+  RT_CUDA(cudaGetLastError());
+  FrameParams fp;
+  std::string err;
+  p.spp_grid = 4;
+  st = make_frame_params(camera, nLights, &p, &fo, fp, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  FrameOut ko;
+  std::memset(&ko, 0, sizeof(ko));
+  ko.pixels = reinterpret_cast<double *>(d_pixels);
+  st = launch(s, fp, reinterpret_cast<const double *>(d_lightsPos), reinterpret_cast<const double *>(d_lightsColor),
+              ko, s->d_list, 0, stx, d_count);
+  if (st != RT_OK) return st;
+  // copy to host (mytracer_gpu.cu:112)
+  if (h_image) RT_CUDA(cudaMemcpyAsync(h_image, d_pixels, npx * sizeof(rt_vec4), cudaMemcpyDeviceToHost, stx));
+  RT_CUDA(cudaStreamSynchronize(stx));
+  return RT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,343 @@
+// rt_flatten.cpp — "GPU-friendly flattening of the reference's BVH" (north star (a)).
+//
+// Input is exactly what the reference hands its kernel: struct Data (mydata.h:28-72, filled by
+// Raytracer::build_Data mytracer.cpp:166-296) and BVH::BVHNodes_SoA (mybvh.h:49-55, built by
+// BVH::initSoA mybvh.cpp:375-406).  The reference never records how many node slots are in use
+// (mybvh.h:57), so the tree is discovered by walking from node 0.  The split topology is kept
+// as is: one 64-byte NodeRec per interior node, children in the reference's left/right order,
+// leaves referencing the same [firstTriIdx_, firstTriIdx_+triCount_) ranges.
+#include "rt_flatten.h"
+#include <cmath>
+#include <cstring>
+#include <initializer_list>
+#include <limits>
+
+namespace rtb {
+namespace {
+
+inline float round_down(double v) {
+  float f = (float)v;
+  if ((double)f > v) f = std::nextafterf(f, -std::numeric_limits<float>::infinity());
+  return f;
+}
+inline float round_up(double v) {
+  float f = (float)v;
+  if ((double)f < v) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+  return f;
+}
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Walk {
+  int ref_node;  // node index in the reference arrays
+  int flat_idx;  // NodeRec index assigned to it
+  int depth;
+};
+
+} // namespace
+
+int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
+                  int num_objects, std::vector<unsigned char> &blob, std::string &err) {
+  if (num_objects < 0 || (num_objects > 0 && !objects)) {
+    err = "flatten: objects pointer/count invalid";
+    return RT_ERR_INVALID_ARG;
+  }
+  const int N = data ? data->tVertexIdxCount_ / 3 : 0;
+  const int num_meshes = data ? data->tMeshCount_ : 0;
+  if (data && (data->tVertexIdxCount_ < 0 || data->tVertexIdxCount_ % 3 != 0 || num_meshes < 0)) {
+    err = "flatten: tVertexIdxCount_ must be a non-negative multiple of 3";
+    return RT_ERR_INVALID_ARG;
+  }
+  if (N > 0) {
+    if (!bvh || !bvh->bb_min_ || !bvh->bb_max_ || !bvh->leftChildIdx_ || !bvh->firstTriIdx_ ||
+        !bvh->triCount_) {
+      err = "flatten: triangles present but BVH arrays missing";
+      return RT_ERR_INVALID_ARG;
+    }
+    if (!data->vertexIdx_ || !data->vertexPos_ || !data->vertexMeshId_ || !data->normals_ ||
+        !data->vertexNormals_ || !data->meshDrawMode_ || !data->meshTexWidth_ || !data->meshTexHeight_ ||
+        !data->materialAmbient_ || !data->materialDiffuse_ || !data->materialSpecular_ ||
+        !data->materialShininess_ || !data->materialMirror_ || !data->materialShadowable_) {
+      err = "flatten: a required Data array is null";
+      return RT_ERR_INVALID_ARG;
+    }
+  }
+
+  // ---- 1. walk the reference tree, number interior nodes in DFS pre-order -------------------
+  std::vector<NodeRec> nodes;
+  int max_depth = 0, max_leaf = 0, nodes_ref = 0, root_is_leaf = 0;
+  std::vector<unsigned char> tri_seen(N > 0 ? N : 0, 0);
+  const int cap = 2 * N - 1; // slots the reference allocates (mybvh.cpp:386)
+  auto box_of = [&](int r, float *mn, float *mx) {
+    const rt_vec4 &a = bvh->bb_min_[r], &b = bvh->bb_max_[r];
+    mn[0] = round_down(a.x); mn[1] = round_down(a.y); mn[2] = round_down(a.z);
+    mx[0] = round_up(b.x);   mx[1] = round_up(b.y);   mx[2] = round_up(b.z);
+  };
+  auto leaf_ok = [&](int r) -> bool {
+    const int f = bvh->firstTriIdx_[r], c = bvh->triCount_[r];
+    if (f < 0 || c <= 0 || f > N - c) return false;
+    for (int i = f; i < f + c; ++i) {
+      if (tri_seen[i]) return false;
+      tri_seen[i] = 1;
+    }
+    if (c > max_leaf) max_leaf = c;
+    return true;
+  };
+  if (N > 0) {
+    if (bvh->triCount_[0] > 0) {
+      // the whole mesh is one leaf (N <= 2 or an unsplittable root): pseudo root with an
+      // empty second child so that the kernel needs no special case
+      root_is_leaf = 1;
+      nodes_ref = 1;
+      if (!leaf_ok(0)) { err = "flatten: root leaf range invalid"; return RT_ERR_BAD_SCENE; }
+      NodeRec n;
+      box_of(0, n.c0_min, n.c0_max);
+      for (int k = 0; k < 3; ++k) n.c1_min[k] = 1e30f, n.c1_max[k] = -1e30f;
+      n.ref0 = bvh->firstTriIdx_[0]; n.cnt0 = bvh->triCount_[0];
+      n.ref1 = 0; n.cnt1 = 0;
+      nodes.push_back(n);
+      max_depth = 1;
+    } else {
+      std::vector<Walk> todo;
+      nodes.emplace_back();
+      todo.push_back({0, 0, 1});
+      nodes_ref = 1;
+      while (!todo.empty()) {
+        const Walk w = todo.back();
+        todo.pop_back();
+        if (w.depth > max_depth) max_depth = w.depth;
+        const int l = bvh->leftChildIdx_[w.ref_node];
+        if (l < 1 || l + 1 > cap - 1) {
+          err = "flatten: child index out of range at node " + std::to_string(w.ref_node);
+          return RT_ERR_BAD_SCENE;
+        }
+        nodes_ref += 2;
+        if (nodes_ref > cap) { err = "flatten: BVH has a cycle or more than 2N-1 nodes"; return RT_ERR_BAD_SCENE; }
+        NodeRec n;
+        box_of(l, n.c0_min, n.c0_max);
+        box_of(l + 1, n.c1_min, n.c1_max);
+        int ref[2], cnt[2];
+        // right child first onto the stack so that the LEFT subtree gets the next indices
+        // (DFS pre-order: a left descent walks contiguous records)
+        int child_flat[2] = {-1, -1};
+        for (int s = 0; s < 2; ++s) {
+          const int r = l + s;
+          if (bvh->triCount_[r] > 0) {
+            if (!leaf_ok(r)) {
+              err = "flatten: leaf range invalid/overlapping at node " + std::to_string(r);
+              return RT_ERR_BAD_SCENE;
+            }
+            ref[s] = bvh->firstTriIdx_[r]; cnt[s] = bvh->triCount_[r];
+            if (w.depth + 1 > max_depth) max_depth = w.depth + 1;
+          } else {
+            child_flat[s] = (int)nodes.size();
+            nodes.emplace_back();
+            ref[s] = child_flat[s]; cnt[s] = 0;
+          }
+        }
+        if (child_flat[1] >= 0) todo.push_back({l + 1, child_flat[1], w.depth + 1});
+        if (child_flat[0] >= 0) todo.push_back({l, child_flat[0], w.depth + 1});
+        n.ref0 = ref[0]; n.cnt0 = cnt[0]; n.ref1 = ref[1]; n.cnt1 = cnt[1];
+        nodes[w.flat_idx] = n;
+      }
+    }
+    for (int i = 0; i < N; ++i)
+      if (!tri_seen[i]) { err = "flatten: triangle " + std::to_string(i) + " is in no leaf"; return RT_ERR_BAD_SCENE; }
+    if (max_depth > kStackMax) {
+      err = "flatten: BVH depth " + std::to_string(max_depth) + " exceeds traversal stack " + std::to_string(kStackMax);
+      return RT_ERR_LIMIT;
+    }
+  }
+
+  // ---- 2. per-triangle records -------------------------------------------------------------
+  std::vector<TriFilter> filt(N);
+  std::vector<TriExact> exact(N);
+  std::vector<TriShade> shade(N);
+  double extent = 0.0;
+  const int nv = data ? data->tVertexCount_ : 0;
+  for (int i = 0; i < N; ++i) {
+    const int v0 = data->vertexIdx_[3 * i], v1 = data->vertexIdx_[3 * i + 1], v2 = data->vertexIdx_[3 * i + 2];
+    if (v0 < 0 || v1 < 0 || v2 < 0 || v0 >= nv || v1 >= nv || v2 >= nv) {
+      err = "flatten: vertex index out of range in triangle " + std::to_string(i);
+      return RT_ERR_BAD_SCENE;
+    }
+    const rt_vec4 &p0 = data->vertexPos_[v0], &p1 = data->vertexPos_[v1], &p2 = data->vertexPos_[v2];
+    const int mesh = data->vertexMeshId_[v0]; // as mytracer_gpu.cu:492
+    if (mesh < 0 || mesh >= num_meshes) {
+      err = "flatten: vertexMeshId_ out of range in triangle " + std::to_string(i);
+      return RT_ERR_BAD_SCENE;
+    }
+    TriExact &e = exact[i];
+    e.p0[0] = p0.x; e.p0[1] = p0.y; e.p0[2] = p0.z;
+    e.p1[0] = p1.x; e.p1[1] = p1.y; e.p1[2] = p1.z;
+    e.p2[0] = p2.x; e.p2[1] = p2.y; e.p2[2] = p2.z;
+    e.mesh = mesh; e.pad = 0;
+    const double e1[3] = {p0.x - p2.x, p0.y - p2.y, p0.z - p2.z};
+    const double e2[3] = {p1.x - p2.x, p1.y - p2.y, p1.z - p2.z};
+    const double a = std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]);
+    const double b = std::sqrt(e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2]);
+    for (const rt_vec4 *p : {&p0, &p1, &p2}) {
+      extent = std::fmax(extent, std::fmax(std::fabs(p->x), std::fmax(std::fabs(p->y), std::fabs(p->z))));
+    }
+    TriFilter &f = filt[i];
+    for (int k = 0; k < 3; ++k) {
+      f.p2[k] = (float)e.p2[k];
+      f.e1[k] = (float)e1[k];
+      f.e2[k] = (float)e2[k];
+    }
+    const double u = 5.9604644775390625e-8; // 2^-24
+    const double tiny = 1e-30;
+    f.k_bary = round_up(std::fmax(8.0 * u * std::fmax(a, b), tiny));
+    f.k_t = round_up(std::fmax(8.0 * u * a * b, tiny));
+    f.k_det = round_up(std::fmax(64.0 * u * a * b, tiny));
+
+    TriShade &s = shade[i];
+    std::memset(&s, 0, sizeof(s));
+    s.mesh = mesh;
+    if (data->meshDrawMode_[mesh] == 0) {
+      const rt_vec4 &n = data->normals_[i];
+      s.n[0] = n.x; s.n[1] = n.y; s.n[2] = n.z;
+    } else {
+      const int vs[3] = {v0, v1, v2};
+      for (int k = 0; k < 3; ++k) {
+        const rt_vec4 &n = data->vertexNormals_[vs[k]];
+        s.n[3 * k] = n.x; s.n[3 * k + 1] = n.y; s.n[3 * k + 2] = n.z;
+      }
+    }
+    if (data->meshTexWidth_[mesh] != -1) {
+      if (!data->textureIdx_ || !data->textureCoordinatesU_ || !data->textureCoordinatesV_) {
+        err = "flatten: textured mesh but texture index/coordinate arrays are null";
+        return RT_ERR_INVALID_ARG;
+      }
+      for (int k = 0; k < 3; ++k) {
+        const int t = data->textureIdx_[3 * i + k];
+        if (t < 0 || t >= data->tTextCoordCount_) {
+          err = "flatten: texture index out of range in triangle " + std::to_string(i);
+          return RT_ERR_BAD_SCENE;
+        }
+        s.uv[2 * k] = data->textureCoordinatesU_[t];
+        s.uv[2 * k + 1] = data->textureCoordinatesV_[t];
+      }
+    }
+  }
+  if (extent > 1e9) {
+    // FP32 products could overflow: disable the filter (everything is confirmed in FP64)
+    for (TriFilter &f : filt) f.k_det = std::numeric_limits<float>::infinity();
+  }
+
+  // ---- 3. meshes, objects, texels ------------------------------------------------------------
+  std::vector<MeshRec> meshes(num_meshes);
+  size_t num_texels = 0;
+  for (int m = 0; m < num_meshes; ++m) {
+    MeshRec &r = meshes[m];
+    std::memset(&r, 0, sizeof(r));
+    const rt_vec4 &ka = data->materialAmbient_[m], &kd = data->materialDiffuse_[m], &ks = data->materialSpecular_[m];
+    r.ambient[0] = ka.x; r.ambient[1] = ka.y; r.ambient[2] = ka.z;
+    r.diffuse[0] = kd.x; r.diffuse[1] = kd.y; r.diffuse[2] = kd.z;
+    r.specular[0] = ks.x; r.specular[1] = ks.y; r.specular[2] = ks.z;
+    r.shininess = data->materialShininess_[m];
+    r.mirror = data->materialMirror_[m];
+    r.shadowable = data->materialShadowable_[m] ? 1 : 0;
+    r.draw_mode = data->meshDrawMode_[m];
+    r.tex_w = data->meshTexWidth_[m];
+    r.tex_h = data->meshTexHeight_[m];
+    if (r.tex_w != -1) {
+      if (r.tex_w <= 0 || r.tex_h <= 0 || !data->meshTexels_ || !data->firstMeshTex_) {
+        err = "flatten: texture of mesh " + std::to_string(m) + " invalid";
+        return RT_ERR_BAD_SCENE;
+      }
+      r.tex_offset = data->firstMeshTex_[m];
+      const size_t end = (size_t)r.tex_offset + (size_t)r.tex_w * r.tex_h;
+      if (end > data->tTexelCount_) {
+        err = "flatten: texture of mesh " + std::to_string(m) + " exceeds tTexelCount_";
+        return RT_ERR_BAD_SCENE;
+      }
+      if (end > num_texels) num_texels = end;
+    }
+  }
+  std::vector<ObjectRec> objs(num_objects);
+  for (int k = 0; k < num_objects; ++k) {
+    const rt_object &o = objects[k];
+    if (o.kind != RT_SPHERE && o.kind != RT_PLANE) { err = "flatten: unknown object kind"; return RT_ERR_INVALID_ARG; }
+    ObjectRec &r = objs[k];
+    std::memset(&r, 0, sizeof(r));
+    r.kind = o.kind;
+    r.shadowable = o.material.shadowable ? 1 : 0;
+    r.center[0] = o.center.x; r.center[1] = o.center.y; r.center[2] = o.center.z;
+    r.normal[0] = o.normal.x; r.normal[1] = o.normal.y; r.normal[2] = o.normal.z;
+    r.radius = o.radius;
+    r.ambient[0] = o.material.ambient.x; r.ambient[1] = o.material.ambient.y; r.ambient[2] = o.material.ambient.z;
+    r.diffuse[0] = o.material.diffuse.x; r.diffuse[1] = o.material.diffuse.y; r.diffuse[2] = o.material.diffuse.z;
+    r.specular[0] = o.material.specular.x; r.specular[1] = o.material.specular.y; r.specular[2] = o.material.specular.z;
+    r.shininess = o.material.shininess;
+    r.mirror = o.material.mirror;
+  }
+
+  // ---- 4. assemble -----------------------------------------------------------------------------
+  BlobHeader h;
+  std::memset(&h, 0, sizeof(h));
+  h.magic = kBlobMagic; h.version = kBlobVersion;
+  h.num_nodes = (int)nodes.size(); h.num_tris = N; h.num_meshes = num_meshes; h.num_objects = num_objects;
+  h.root_is_leaf = root_is_leaf; h.max_depth = max_depth; h.max_leaf = max_leaf; h.num_nodes_ref = nodes_ref;
+  h.num_texels = num_texels;
+  h.scene_extent = (float)extent;
+  size_t off = align_up(sizeof(BlobHeader), kSectionAlign);
+  h.off_nodes = off;   off = align_up(off + nodes.size() * sizeof(NodeRec), kSectionAlign);
+  h.off_filter = off;  off = align_up(off + filt.size() * sizeof(TriFilter), kSectionAlign);
+  h.off_exact = off;   off = align_up(off + exact.size() * sizeof(TriExact), kSectionAlign);
+  h.off_shade = off;   off = align_up(off + shade.size() * sizeof(TriShade), kSectionAlign);
+  h.off_meshes = off;  off = align_up(off + meshes.size() * sizeof(MeshRec), kSectionAlign);
+  h.off_objects = off; off = align_up(off + objs.size() * sizeof(ObjectRec), kSectionAlign);
+  h.off_texels = off;  off = align_up(off + num_texels * 4 * sizeof(float), kSectionAlign);
+  h.total_bytes = off;
+  blob.assign(off, 0);
+  std::memcpy(blob.data(), &h, sizeof(h));
+  if (!nodes.empty()) std::memcpy(blob.data() + h.off_nodes, nodes.data(), nodes.size() * sizeof(NodeRec));
+  if (N > 0) {
+    std::memcpy(blob.data() + h.off_filter, filt.data(), filt.size() * sizeof(TriFilter));
+    std::memcpy(blob.data() + h.off_exact, exact.data(), exact.size() * sizeof(TriExact));
+    std::memcpy(blob.data() + h.off_shade, shade.data(), shade.size() * sizeof(TriShade));
+  }
+  if (num_meshes > 0) std::memcpy(blob.data() + h.off_meshes, meshes.data(), meshes.size() * sizeof(MeshRec));
+  if (num_objects > 0) std::memcpy(blob.data() + h.off_objects, objs.data(), objs.size() * sizeof(ObjectRec));
+  float *tx = reinterpret_cast<float *>(blob.data() + h.off_texels);
+  for (size_t t = 0; t < num_texels; ++t) {
+    const rt_vec4 &c = data->meshTexels_[t];
+    tx[4 * t] = (float)c.x; tx[4 * t + 1] = (float)c.y; tx[4 * t + 2] = (float)c.z; tx[4 * t + 3] = 1.0f;
+  }
+  return RT_OK;
+}
+
+int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
+  if (!blob || bytes < sizeof(BlobHeader)) { err = "blob: too small"; return RT_ERR_INVALID_ARG; }
+  BlobHeader h;
+  std::memcpy(&h, blob, sizeof(h));
+  if (h.magic != kBlobMagic || h.version != kBlobVersion) { err = "blob: bad magic/version"; return RT_ERR_BAD_SCENE; }
+  if (h.total_bytes != bytes) { err = "blob: size mismatch"; return RT_ERR_BAD_SCENE; }
+  const bool ok = h.off_nodes + (size_t)h.num_nodes * sizeof(NodeRec) <= h.off_filter &&
+                  h.off_filter + (size_t)h.num_tris * sizeof(TriFilter) <= h.off_exact &&
+                  h.off_exact + (size_t)h.num_tris * sizeof(TriExact) <= h.off_shade &&
+                  h.off_shade + (size_t)h.num_tris * sizeof(TriShade) <= h.off_meshes &&
+                  h.off_meshes + (size_t)h.num_meshes * sizeof(MeshRec) <= h.off_objects &&
+                  h.off_objects + (size_t)h.num_objects * sizeof(ObjectRec) <= h.off_texels &&
+                  h.off_texels + h.num_texels * 16 <= h.total_bytes;
+  if (!ok) { err = "blob: section table inconsistent"; return RT_ERR_BAD_SCENE; }
+  return RT_OK;
+}
+
+SceneView view_of_blob(const unsigned char *blob) {
+  BlobHeader h;
+  std::memcpy(&h, blob, sizeof(h));
+  SceneView v;
+  v.nodes = reinterpret_cast<const NodeRec *>(blob + h.off_nodes);
+  v.filt = reinterpret_cast<const TriFilter *>(blob + h.off_filter);
+  v.exact = reinterpret_cast<const TriExact *>(blob + h.off_exact);
+  v.shade = reinterpret_cast<const TriShade *>(blob + h.off_shade);
+  v.meshes = reinterpret_cast<const MeshRec *>(blob + h.off_meshes);
+  v.objects = reinterpret_cast<const ObjectRec *>(blob + h.off_objects);
+  v.texels = reinterpret_cast<const float *>(blob + h.off_texels);
+  v.tex_objs = nullptr;
+  v.num_nodes = h.num_nodes; v.num_tris = h.num_tris; v.num_meshes = h.num_meshes; v.num_objects = h.num_objects;
+  return v;
+}
+
+} // namespace rtb

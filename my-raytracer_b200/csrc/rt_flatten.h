@@ -1,0 +1,22 @@
+// rt_flatten.h — host flattener: reference Data SoA + BVHNodes_SoA -> one HBM blob (rt_types.h).
+#ifndef RTB_FLATTEN_H
+#define RTB_FLATTEN_H
+#include "../../include/rt_b200.h"
+#include "rt_types.h"
+#include <string>
+#include <vector>
+
+namespace rtb {
+
+// Returns RT_OK or an rt_status; on failure `err` holds the message.
+int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
+                  int num_objects, std::vector<unsigned char> &blob, std::string &err);
+
+// Validates a blob received from another rank (magic, version, section bounds).
+int check_blob(const unsigned char *blob, size_t bytes, std::string &err);
+
+// Host-side view of a blob (pointers into `blob`); tex_objs is left null.
+SceneView view_of_blob(const unsigned char *blob);
+
+} // namespace rtb
+#endif

@@ -1,0 +1,119 @@
+// rt_kernel.cuh — the sm_100a render kernel: persistent warps, warp-level work fetch.
+//
+// Replaces compute_image_device (mytracer_gpu.cu:119-160: one thread per pixel, 16x16 blocks,
+// FP64 recursion-free but stack-in-local-memory traversal).  Here:
+//   * the grid is sized to the machine (SM count x resident CTAs), not to the image;
+//   * each warp keeps all 32 lanes busy: whenever lanes go idle, lane 0 claims that many work
+//     slots with ONE atomicAdd and the slots are handed out by __ballot/__popc rank
+//     (north star (b): "warp-level work fetch (atomics plus __shfl / __ballot)");
+//   * work slots follow 8x4-pixel tiles so that a freshly filled warp covers a compact screen
+//     patch (coherent primary rays);
+//   * every lane runs the rt_core.cuh state machine; the traversal loop is shared by primary,
+//     shadow and reflection rays.
+#ifndef RTB_KERNEL_CUH
+#define RTB_KERNEL_CUH
+#include "rt_core.cuh"
+#include <cuda_runtime.h>
+
+namespace rtb {
+
+constexpr int kBlockThreads = 128;
+constexpr unsigned kFullMask = 0xffffffffu;
+
+struct KernelArgs {
+  SceneView sv;
+  FrameParams fp;
+  const double *light_pos;
+  const double *light_col;
+  FrameOut out;
+  const int *pixel_list;
+  int list_count;
+  const int *list_count_ptr;        // optional: list length produced on the device (no host sync)
+  unsigned long long *work_counter; // zeroed before every launch
+  unsigned long long *counters;     // C_COUNT entries (COUNT builds)
+};
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlockThreads) render_kernel(const __grid_constant__ KernelArgs a) {
+  unsigned int cnt[COUNT ? C_COUNT : 1];
+  if (COUNT) {
+#pragma unroll
+    for (int k = 0; k < C_COUNT; ++k) cnt[k] = 0;
+  }
+  Ctx c;
+  c.sv = a.sv; c.fp = a.fp;
+  c.light_pos = a.light_pos; c.light_col = a.light_col;
+  c.out = a.out;
+  c.pixel_list = a.pixel_list;
+  c.list_count = a.list_count_ptr ? *a.list_count_ptr : a.list_count;
+  c.cnt = cnt;
+
+  int stk[kStackMax];
+  Lane L;
+  L.mode = M_IDLE;
+  L.node = -1;
+  const long long slots = work_slots(c);
+  const unsigned lane = threadIdx.x & 31u;
+  bool exhausted = false; // warp-uniform
+
+  while (true) {
+    // ---- phase A: path logic for lanes whose traversal finished ---------------------------
+    if (L.mode != M_IDLE && L.node < 0) advance<COUNT>(c, L);
+
+    // ---- warp-level work fetch for idle lanes ----------------------------------------------
+    const unsigned idle = __ballot_sync(kFullMask, L.mode == M_IDLE);
+    if (idle != 0u && !exhausted) {
+      const int n = __popc(idle);
+      const int leader = __ffs(idle) - 1;
+      unsigned long long base = 0;
+      if ((int)lane == leader) base = atomicAdd(a.work_counter, (unsigned long long)n);
+      base = __shfl_sync(kFullMask, base, leader);
+      if ((long long)base >= slots) {
+        exhausted = true;
+      } else if (L.mode == M_IDLE) {
+        const long long mine = (long long)base + __popc(idle & ((1u << lane) - 1u));
+        int px, py;
+        if (mine < slots && work_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, L, px, py);
+      }
+    }
+    const unsigned busy = __ballot_sync(kFullMask, L.mode != M_IDLE);
+    if (busy == 0u) {
+      if (exhausted) break;
+      continue;
+    }
+    // ---- phase B: one traversal loop for every ray type -------------------------------------
+    while (__any_sync(kFullMask, L.node >= 0)) {
+      if (L.node >= 0) trav_step<COUNT>(c, L, stk);
+    }
+  }
+  if (COUNT) {
+#pragma unroll
+    for (int k = 0; k < C_COUNT; ++k)
+      if (cnt[k]) atomicAdd(a.counters + k, (unsigned long long)cnt[k]);
+  }
+}
+
+// Contrast test of the adaptive supersampling pass (adaptive_supersampling_device,
+// mytracer_gpu.cu:162-229): interior pixels whose summed squared colour distance to the 4-neighbourhood
+// exceeds `threshold` are appended to `list`; a second render_kernel launch re-renders exactly those
+// pixels with a subp x subp sample grid (a compaction instead of the reference's mostly-idle full grid).
+__global__ void flag_contrast_kernel(const double *__restrict__ pixels, int width, int height, double threshold,
+                                     int *__restrict__ list, int *__restrict__ count) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= width - 1 || y >= height - 1 || x < 1 || y < 1) return;
+  const size_t p = (size_t)y * width + x;
+  const D3 c = ld3(pixels + 4 * p);
+  auto dist2 = [&](size_t q) {
+    const D3 d = sub(c, ld3(pixels + 4 * q));
+    return dot(d, d);
+  };
+  const double n = dadd(dadd(dadd(dist2(p + 1), dist2(p + width)), dist2(p - 1)), dist2(p - width));
+  if (n > threshold) {
+    const int slot = atomicAdd(count, 1);
+    list[slot] = (int)p;
+  }
+}
+
+} // namespace rtb
+#endif

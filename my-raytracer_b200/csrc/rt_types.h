@@ -1,0 +1,140 @@
+// rt_types.h — layout of the flattened scene blob in HBM (shared by the host flattener,
+// the CUDA kernel and the host-compiled test build of the kernel core).
+//
+// One contiguous, 512-byte-sectioned blob (so it can be broadcast with a single NCCL call):
+//
+//   BlobHeader | NodeRec[] | TriFilter[] | TriExact[] | TriShade[] | MeshRec[] | ObjectRec[] | texels
+//
+// * NodeRec   64 B  (4 x float4): one record per INTERIOR node of the reference's median-split
+//             tree (mybvh.h:49-55 / mybvh.cpp:438-472) holding BOTH child boxes, outward-
+//             rounded to FP32, plus the two child references.  Same topology, half the
+//             dependent loads of the reference's 76 B/node five-array layout.
+// * TriFilter 48 B  (3 x float4): FP32 Moeller-Trumbore operands + per-triangle error-bound
+//             constants, BVH order.  A conservative filter: it never rejects a triangle the
+//             reference's FP64 test (mymesh.cpp:176-236) accepts.
+// * TriExact  80 B  (5 x 16 B): the three vertex positions in FP64, read only for filter
+//             survivors; the confirmation reproduces the reference arithmetic bit for bit.
+// * TriShade 128 B: normals (face or 3 vertex normals), UVs, mesh id — read once per shaded hit.
+// * MeshRec  128 B: material + draw mode + texture descriptor (mydata.h:57-71).
+// * ObjectRec: analytic primitives (Raytracer::objects_), FP64.
+#ifndef RTB_TYPES_H
+#define RTB_TYPES_H
+#include <stddef.h>
+#include <stdint.h>
+
+namespace rtb {
+
+constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
+constexpr uint32_t kBlobVersion = 3;
+constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
+constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
+constexpr size_t kSectionAlign = 512;
+
+struct alignas(16) NodeRec {
+  // c0 = left child (leftChildIdx_), c1 = right child (leftChildIdx_ + 1)
+  float c0_min[3], c0_max[3];
+  float c1_min[3], c1_max[3];
+  // ref >= 0.  cnt == 0: ref is the NodeRec index of an interior child.
+  //            cnt  > 0: leaf child with triangles [ref, ref + cnt) in BVH order.
+  int32_t ref0, ref1, cnt0, cnt1;
+};
+static_assert(sizeof(NodeRec) == 64, "NodeRec must be 64 bytes");
+
+struct alignas(16) TriFilter {
+  float p2[3], k_bary; // vertex p2 ; 8u*max(|e1|,|e2|)   (bound on the U,V numerators, per unit rho)
+  float e1[3], k_t;    // p0 - p2   ; 8u*|e1||e2|         (bound on the t numerator, per unit rho)
+  float e2[3], k_det;  // p1 - p2   ; 64u*|e1||e2|        (bound on the determinant)
+};
+static_assert(sizeof(TriFilter) == 48, "TriFilter must be 48 bytes");
+
+struct alignas(16) TriExact {
+  double p0[3], p1[3], p2[3];
+  int32_t mesh, pad;
+};
+static_assert(sizeof(TriExact) == 80, "TriExact must be 80 bytes");
+
+struct alignas(16) TriShade {
+  double n[9];  // FLAT: n[0..2] = face normal (Data::normals_); PHONG: the 3 vertex normals
+  double uv[6]; // u0 v0 u1 v1 u2 v2 (zeros when the mesh has no texture)
+  int32_t mesh, pad;
+};
+static_assert(sizeof(TriShade) == 128, "TriShade must be 128 bytes");
+
+struct alignas(16) MeshRec {
+  double ambient[3], diffuse[3], specular[3];
+  double shininess, mirror;
+  int32_t shadowable, draw_mode; // draw_mode 0 FLAT, 1 PHONG (mytracer_gpu.cu:498-501)
+  int32_t tex_w, tex_h;          // -1 when untextured (mytracer.cpp:273-275)
+  uint64_t tex_offset;           // first texel (float4 index) inside the blob's texel section
+  uint64_t pad;
+};
+static_assert(sizeof(MeshRec) == 128, "MeshRec must be 128 bytes");
+
+struct alignas(16) ObjectRec {
+  int32_t kind, shadowable; // kind 0 sphere, 1 plane
+  double center[3];
+  double normal[3];
+  double radius;
+  double ambient[3], diffuse[3], specular[3];
+  double shininess, mirror;
+  double pad;
+};
+static_assert(sizeof(ObjectRec) == 160, "ObjectRec must be 160 bytes");
+
+struct BlobHeader {
+  uint32_t magic, version;
+  uint64_t total_bytes;
+  int32_t num_nodes, num_tris, num_meshes, num_objects;
+  int32_t root_is_leaf, max_depth, max_leaf, num_nodes_ref;
+  uint64_t num_texels;
+  uint64_t off_nodes, off_filter, off_exact, off_shade, off_meshes, off_objects, off_texels;
+  float scene_extent; // max |coordinate| over all vertices (diagnostics)
+  float pad_f[3];
+  uint64_t reserved[6];
+};
+static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
+
+// Pointers into a resident blob (device pointers in the kernel, host pointers in the test build).
+struct SceneView {
+  const NodeRec *nodes;
+  const TriFilter *filt;
+  const TriExact *exact;
+  const TriShade *shade;
+  const MeshRec *meshes;
+  const ObjectRec *objects;
+  const float *texels; // 4 floats per texel (host/test build); the kernel uses tex_objs instead
+  const unsigned long long *tex_objs; // cudaTextureObject_t per mesh (0 when untextured)
+  int32_t num_nodes, num_tris, num_meshes, num_objects;
+};
+
+struct CameraRec {
+  double eye[3], x_dir[3], y_dir[3], lower_left[3];
+  int32_t width, height;
+};
+
+struct FrameParams {
+  CameraRec cam;
+  double background[3], ambience[3];
+  int32_t max_depth, spp_grid;
+  int32_t num_lights;
+  int32_t tile_rank, tile_world, tile_chunk;
+  int32_t tiles_x, tiles_y;
+  int32_t flags;
+  int32_t pad;
+};
+
+struct FrameOut {
+  uint8_t *rgba8;
+  double *pixels; // 4 doubles per pixel
+  int32_t *hit_id;
+  double *hit_t;
+};
+
+// indices into the counters array (RT_FLAG_COUNTERS build)
+enum Counter {
+  C_RAY_PRIMARY = 0, C_RAY_SHADOW, C_RAY_REFLECT, C_BOX, C_TRI_FILTER, C_TRI_EXACT, C_OBJECT,
+  C_SHADED, C_TEXEL, C_NODES, C_COUNT
+};
+
+} // namespace rtb
+#endif

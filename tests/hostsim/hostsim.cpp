@@ -1,0 +1,132 @@
+// TEST INFRASTRUCTURE — host-compiled build of the kernel core (rt_core.cuh).
+//
+// This container has no GPU; this library lets the CPU test-suite run the SAME per-lane state
+// machine, flattener and host prep code that the CUDA kernel uses, one lane at a time, and compare
+// it with the oracle before GPU minutes are spent.  It is NOT a product path: nothing in
+// my-raytracer_b200/ loads it, the C-ABI library never falls back to it, and bench.py never
+// times it.
+#include "../../my-raytracer_b200/csrc/rt_core.cuh"
+#include "../../my-raytracer_b200/csrc/rt_flatten.h"
+#include "../../my-raytracer_b200/csrc/rt_frame.h"
+#include <cstdlib>
+#include <omp.h>
+#include <vector>
+
+namespace rtb {
+static thread_local std::string g_err;
+void set_error(const std::string &m) { g_err = m; }
+} // namespace rtb
+
+extern "C" {
+
+const char *sim_last_error(void) { return rtb::g_err.c_str(); }
+
+int sim_flatten(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects, int nobj,
+                unsigned char **blob_out, size_t *bytes) {
+  std::vector<unsigned char> blob;
+  std::string err;
+  const int st = rtb::flatten_scene(data, bvh, objects, nobj, blob, err);
+  if (st != RT_OK) { rtb::set_error(err); return st; }
+  *blob_out = (unsigned char *)std::malloc(blob.size());
+  std::memcpy(*blob_out, blob.data(), blob.size());
+  *bytes = blob.size();
+  return RT_OK;
+}
+void sim_free(void *p) { std::free(p); }
+
+int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, const rt_vec4 *lpos,
+               const rt_vec4 *lcol, int nlights, const rt_render_params *params, const rt_frame_out *out,
+               unsigned long long *counters, int nthreads) {
+  using namespace rtb;
+  std::string err;
+  int st = check_blob(blob, bytes, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  Ctx c;
+  st = make_frame_params(cam, nlights, params, out, c.fp, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  c.sv = view_of_blob(blob);
+  c.light_pos = reinterpret_cast<const double *>(lpos);
+  c.light_col = reinterpret_cast<const double *>(lcol);
+  c.pixel_list = nullptr;
+  c.list_count = 0;
+  c.out.rgba8 = out->rgba8;
+  c.out.pixels = reinterpret_cast<double *>(out->pixels);
+  c.out.hit_id = out->hit_id;
+  c.out.hit_t = out->hit_t;
+  const long long slots = work_slots(c);
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+  std::vector<unsigned long long> total(C_COUNT, 0);
+#pragma omp parallel
+  {
+    unsigned int cnt[C_COUNT] = {0};
+    unsigned long long mine[C_COUNT] = {0};
+    Ctx ct = c;
+    ct.cnt = cnt;
+    int stk[kStackMax];
+#pragma omp for schedule(dynamic, 256)
+    for (long long w = 0; w < slots; ++w) {
+      int px, py;
+      if (!work_to_pixel(ct, w, px, py)) continue;
+      Lane L;
+      L.mode = M_IDLE; L.node = -1;
+      begin_pixel<true>(ct, L, px, py);
+      while (L.mode != M_IDLE) {
+        if (L.node >= 0) trav_step<true>(ct, L, stk);
+        else advance<true>(ct, L);
+      }
+      for (int k = 0; k < C_COUNT; ++k) { mine[k] += cnt[k]; cnt[k] = 0; }
+    }
+#pragma omp critical
+    for (int k = 0; k < C_COUNT; ++k) total[k] += mine[k];
+  }
+  if (counters) for (int k = 0; k < C_COUNT; ++k) counters[k] = total[k];
+  return RT_OK;
+}
+
+// direct access to the primitives for property tests
+int sim_tri_filter(const double *p0, const double *p1, const double *p2, const double *o, const double *d,
+                   double thi) {
+  using namespace rtb;
+  // build the record exactly like the flattener does
+  TriFilter f;
+  const double e1[3] = {p0[0] - p2[0], p0[1] - p2[1], p0[2] - p2[2]};
+  const double e2[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+  const double a = std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]);
+  const double b = std::sqrt(e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2]);
+  for (int k = 0; k < 3; ++k) { f.p2[k] = (float)p2[k]; f.e1[k] = (float)e1[k]; f.e2[k] = (float)e2[k]; }
+  const double u = 5.9604644775390625e-8, tiny = 1e-30;
+  auto up = [](double v) { float x = (float)v; if ((double)x < v) x = nextafterf(x, INFINITY); return x; };
+  f.k_bary = up(std::fmax(8.0 * u * std::fmax(a, b), tiny));
+  f.k_t = up(std::fmax(8.0 * u * a * b, tiny));
+  f.k_det = up(std::fmax(64.0 * u * a * b, tiny));
+  RayF r;
+  rayf_setup(r, ld3(o), ld3(d));
+  const float t = fminf(f_up(thi) * (1.0f + 8.0f * kU32), FLT_MAX);
+  return tri_filter(r, f, t) ? 1 : 0;
+}
+
+int sim_tri_exact(const double *p0, const double *p1, const double *p2, const double *o, const double *d,
+                  double *out4) {
+  using namespace rtb;
+  TriHit h;
+  const bool hit = tri_exact(ld3(o), ld3(d), ld3(p0), ld3(p1), ld3(p2), h);
+  if (hit) { out4[0] = h.t; out4[1] = h.alpha; out4[2] = h.beta; out4[3] = h.gamma; }
+  return hit ? 1 : 0;
+}
+
+// conservative FP32 box test against an FP64 box (rounded outward like the flattener)
+int sim_box_test(const double *bmin, const double *bmax, const double *o, const double *d, double thi) {
+  using namespace rtb;
+  float mn[3], mx[3];
+  for (int k = 0; k < 3; ++k) {
+    mn[k] = (float)bmin[k]; if ((double)mn[k] > bmin[k]) mn[k] = nextafterf(mn[k], -INFINITY);
+    mx[k] = (float)bmax[k]; if ((double)mx[k] < bmax[k]) mx[k] = nextafterf(mx[k], INFINITY);
+  }
+  RayF r;
+  rayf_setup(r, ld3(o), ld3(d));
+  float tn;
+  const float t = fminf(f_up(thi) * (1.0f + 8.0f * kU32), FLT_MAX);
+  return box_test(r, mn, mx, t, tn) ? 1 : 0;
+}
+
+} // extern "C"
