@@ -399,10 +399,13 @@ def textured(width=1920, height=1080, tex_size=1024, slices=224, stacks=112, see
         u = u * 1.1 - 0.05
         tex = value_noise_texture(tex_size, seed + bi, base=col, amp=0.6)
         meshes.append(MeshDesc(pos, idx, skin, 1, idx.copy(), u, v, tex))
+    # ground: gently rolling height field (no coplanar runs, see office()), sky: one quad
     pos, idx, u, v = grid_quad((-8, 0, -6), (16, 0, 0), (0, 0, 12), 64, 48, with_uv=True)
+    pos = pos.copy()
+    pos[:, 1] += 0.05 * np.sin(1.7 * pos[:, 0]) * np.cos(1.3 * pos[:, 2]) + 0.02 * np.sin(5.1 * pos[:, 0] + 3.3 * pos[:, 2])
     meshes.append(MeshDesc(pos, idx, material((0.2, 0.2, 0.2), (1, 1, 1), (0.1, 0.1, 0.1), 10.0, 0.0), 0, idx.copy(),
                            u, v, value_noise_texture(tex_size, seed + 7, base=(0.3, 0.6, 0.3), amp=0.5)))
-    pos, idx, u, v = grid_quad((-20, -2, -9), (40, 0, 0), (0, 22, 0), 8, 8, with_uv=True)
+    pos, idx, u, v = grid_quad((-20, -2, -9), (40, 0, 0), (0, 22, 0), 1, 1, with_uv=True)
     meshes.append(MeshDesc(pos, idx, material((0.9, 0.9, 0.9), (0.2, 0.2, 0.2), (0, 0, 0), 1.0, 0.0, shadowable=False),
                            0, idx.copy(), u, v, value_noise_texture(tex_size // 2, seed + 9, base=(0.4, 0.6, 0.9), amp=0.3)))
     lights = [((6.0, 10.0, 8.0), (0.7, 0.7, 0.7)), ((-7.0, 6.0, 5.0), (0.3, 0.3, 0.35))]
@@ -438,6 +441,8 @@ def scatter(width=3840, height=2160, n_objects=10000, slices=25, stacks=21, seed
             c = cols[chunk[0]]
             meshes.append(MeshDesc(pos, idx, material(0.2 * c, c, (0.6, 0.6, 0.6), 60.0, mir), 1))
     pos, idx = grid_quad((-80, 0, -80), (160, 0, 0), (0, 0, 120), 64, 64)
+    pos = pos.copy()
+    pos[:, 1] += 0.3 * np.sin(0.11 * pos[:, 0]) * np.cos(0.13 * pos[:, 2]) + 0.1 * np.sin(0.7 * pos[:, 0] + 0.5 * pos[:, 2])
     meshes.append(MeshDesc(pos, idx, material((0.2, 0.2, 0.2), (0.5, 0.5, 0.5), (0.1, 0.1, 0.1), 10.0, 0.0), 0))
     lights = [((40.0, 80.0, 60.0), (0.7, 0.7, 0.7)), ((-50.0, 60.0, 30.0), (0.4, 0.4, 0.4))]
     cam = dict(eye=(0.0, 14.0, 55.0), center=(0.0, 4.0, -10.0), up=(0.0, 1.0, 0.0), fovy=50.0, width=width, height=height)
