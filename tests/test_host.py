@@ -1,0 +1,181 @@
+"""Host-side logic of the product (CPU): C-ABI surface, the BVH/normal/camera mirrors against the
+oracle, the flattener's structure and validation, tile sharding arithmetic, and the no-GPU error."""
+import ast
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT
+
+
+def test_cabi_exports_every_declared_symbol(rt, lib):
+    from my_raytracer_b200 import capi
+    hdr = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    declared = set(re.findall(r"^(?:int|const char \*)\s*(rt_[a-z_0-9]+)\(", hdr, re.M))
+    assert declared == set(capi.PROTOTYPES), declared ^ set(capi.PROTOTYPES)
+    for name in declared:
+        assert hasattr(lib, name)
+    assert lib.rt_abi_version() == 1
+
+
+def test_struct_layouts_match_reference_headers(rt):
+    """rt_data_soa / rt_bvh_nodes_soa are field-for-field mirrors of struct Data (mydata.h:28-72) and
+    BVH::BVHNodes_SoA (mybvh.h:49-55): 5 ints + size_t + 27 pointers, and 5 pointers."""
+    from my_raytracer_b200 import capi
+    assert C.sizeof(capi.Vec4) == 32
+    assert C.sizeof(capi.DataSoA) == 24 + 8 + 27 * 8
+    assert C.sizeof(capi.BvhNodesSoA) == 5 * 8
+    assert capi.DataSoA.vertexMeshId_.offset == 32 and capi.DataSoA.materialShadowable_.offset == 32 + 26 * 8
+
+
+def test_no_gpu_fails_loudly(rt, lib):
+    """Without a CUDA device every device entry point reports RT_ERR_NO_DEVICE: no CPU fallback."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from my_raytracer_b200 import capi
+    assert lib.rt_init_device(0) == capi.RT_ERR_NO_DEVICE
+    assert b"no CPU fallback" in lib.rt_last_error()
+    host = rt.HostScene(rt.scenes.mixed_small(width=8, height=8), lib)
+    with pytest.raises(capi.RtError) as e:
+        rt.DeviceScene(host)
+    assert e.value.status == capi.RT_ERR_NO_DEVICE
+
+
+@pytest.mark.parametrize("name", ["mixed_small", "office", "rings", "textured"])
+def test_bvh_build_matches_reference(rt, lib, name):
+    """rt_bvh_build_median == BVH::initSoA/init: node arrays, bounds and triangle permutation."""
+    g = np.load(os.path.join(GOLDEN, f"scene_{name}.npz"))
+    desc = rt.scenes.REGISTRY[name](**ast.literal_eval(str(g["kwargs"])))
+    host = rt.HostScene(desc, lib)
+    n = host.nodes_used
+    assert n == g["bvh_left"].shape[0]
+    b = host.bvh_arrays
+    interior = g["bvh_count"] == 0
+    assert np.array_equal(b["count"][:n], g["bvh_count"])
+    assert np.array_equal(b["left"][:n][interior], g["bvh_left"][interior])
+    assert np.array_equal(b["first"][:n][~interior], g["bvh_first"][~interior])
+    assert np.array_equal(b["bbmin"][:n, :3], g["bvh_min"]) and np.array_equal(b["bbmax"][:n, :3], g["bvh_max"])
+    # the permuted vertexIdx_ rows are the original rows in the reference's BVH order
+    assert np.array_equal(host.arrays["vertexIdx"].reshape(-1, 3), host._orig_vidx[g["tri_order"]])
+
+
+def test_normals_and_camera_match_oracle(rt, lib, orc, oracle_kind):
+    desc = rt.scenes.mixed_small(width=40, height=30)
+    host = rt.HostScene(desc, lib)
+    o = orc.OracleScene(desc, oracle_kind)
+    order = o.tri_order()
+    fn_all = np.concatenate([o.normals(m)[0] for m in range(len(desc.meshes))], 0)
+    vn_all = np.concatenate([o.normals(m)[1] for m in range(len(desc.meshes))], 0)
+    assert np.array_equal(host.arrays["normals"][:, :3], fn_all[order], equal_nan=True)
+    assert np.array_equal(host.arrays["vertexNormals"][:, :3], vn_all, equal_nan=True)
+    cam = host.camera
+    mine = np.array([[v.x, v.y, v.z] for v in (cam.eye, cam.x_dir, cam.y_dir, cam.lower_left)])
+    assert np.array_equal(mine, o.camera())
+
+
+def test_build_data_offsets(rt, lib):
+    """build_Data mirror (mytracer.cpp:166-296): global vertex/uv ids, per-mesh tables, texel layout."""
+    desc = rt.scenes.mixed_small(width=8, height=8)
+    host = rt.HostScene(desc, lib)
+    a = host.arrays
+    nv = [m.pos.shape[0] for m in desc.meshes]
+    assert list(a["firstVertex"]) == list(np.cumsum([0] + nv[:-1])) and list(a["vertexCount"]) == nv
+    assert list(a["vertexIdxCount"]) == [3 * m.idx.shape[0] for m in desc.meshes]
+    assert list(a["texW"]) == [64, -1, -1, -1] and a["firstMeshTex"][0] == 0
+    vid = a["vertexIdx"].reshape(-1, 3)
+    assert ((a["vertexMeshId"][vid[:, 0]] == a["vertexMeshId"][vid[:, 1]]) &
+            (a["vertexMeshId"][vid[:, 0]] == a["vertexMeshId"][vid[:, 2]])).all()
+    tex = desc.meshes[0].tex
+    assert np.array_equal(a["texels"][5 * 64 + 7, :3], tex[5, 7])
+
+
+def _blob_sections(blob):
+    import struct
+    magic, ver, total = struct.unpack_from("<IIQ", blob, 0)
+    ints = struct.unpack_from("<8i", blob, 16)
+    ntex, = struct.unpack_from("<Q", blob, 48)
+    offs = struct.unpack_from("<7Q", blob, 56)
+    return dict(magic=magic, version=ver, total=total, num_nodes=ints[0], num_tris=ints[1], num_meshes=ints[2],
+                num_objects=ints[3], root_is_leaf=ints[4], max_depth=ints[5], max_leaf=ints[6], num_nodes_ref=ints[7],
+                num_texels=ntex, offs=offs)
+
+
+def test_flatten_structure(rt, lib, sim):
+    """Same split topology: every leaf range of the reference tree appears exactly once, boxes are
+    outward-rounded supersets of the FP64 boxes."""
+    desc = rt.scenes.office(width=16, height=9)
+    host = rt.HostScene(desc, lib)
+    blob = sim.flatten(host)
+    h = _blob_sections(blob)
+    n = host.nodes_used
+    cnt = host.bvh_arrays["count"][:n]
+    assert h["total"] == len(blob) and h["num_tris"] == 34000 and h["num_nodes_ref"] == n
+    assert h["num_nodes"] == int((cnt == 0).sum()) and h["max_leaf"] == int(cnt.max())
+    nodes = np.frombuffer(blob, np.float32, h["num_nodes"] * 16, h["offs"][0]).reshape(-1, 16)
+    refs = nodes[:, 12:16].view(np.int32)
+    leaves = set()
+    for r0, r1, c0, c1 in refs:
+        if c0 > 0: leaves.add((int(r0), int(c0)))
+        if c1 > 0: leaves.add((int(r1), int(c1)))
+    first = host.bvh_arrays["first"][:n]
+    assert leaves == {(int(f), int(c)) for f, c in zip(first[cnt > 0], cnt[cnt > 0])}
+    # root record = the two children of reference node 0, conservatively rounded
+    l = host.bvh_arrays["left"][0]
+    mn, mx = host.bvh_arrays["bbmin"], host.bvh_arrays["bbmax"]
+    assert (nodes[0, 0:3] <= mn[l, :3]).all() and (nodes[0, 3:6] >= mx[l, :3]).all()
+    assert (nodes[0, 6:9] <= mn[l + 1, :3]).all() and (nodes[0, 9:12] >= mx[l + 1, :3]).all()
+    assert np.abs(nodes[0, 0:3] - mn[l, :3]).max() < 1e-5
+
+
+def test_flatten_rejects_bad_input(rt, lib, sim):
+    desc = rt.scenes.mixed_small(width=8, height=8)
+    host = rt.HostScene(desc, lib)
+    host.bvh_arrays["left"][0] = 0                       # cycle: root is its own child
+    with pytest.raises(RuntimeError, match="out of range|cycle"):
+        sim.flatten(host)
+    host = rt.HostScene(desc, lib)
+    host.arrays["vertexIdx"][0] = 10**6
+    with pytest.raises(RuntimeError, match="vertex index"):
+        sim.flatten(host)
+    host = rt.HostScene(desc, lib)
+    leafs = np.nonzero(host.bvh_arrays["count"][:host.nodes_used] > 0)[0]
+    host.bvh_arrays["first"][leafs[3]] = host.bvh_arrays["first"][leafs[2]]   # overlapping leaves
+    with pytest.raises(RuntimeError, match="leaf"):
+        sim.flatten(host)
+
+
+def test_flatten_edge_scenes(rt, lib, sim):
+    """empty scene, analytic-only scene, 1-triangle and 2-triangle meshes (root is a leaf)."""
+    empty = rt.SceneDesc("empty", [], [], [], dict(eye=(0, 0, 5), center=(0, 0, 0), up=(0, 1, 0), fovy=40, width=8, height=8))
+    r = sim.render(rt.HostScene(empty, lib))
+    assert (r["hit_id"] == -1).all() and (r["rgba8"][..., :3] == 0).all()
+    for ntri in (1, 2):
+        pos = np.array([[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0.0]])
+        idx = np.array([[0, 1, 2], [0, 2, 3]], np.int32)[:ntri]
+        d = rt.SceneDesc("tiny", [rt.MeshDesc(pos, idx, rt.material((1, 1, 1), (1, 1, 1), (0, 0, 0), 1.0))], [],
+                         [((0, 0, 5), (1, 1, 1))], dict(eye=(0, 0, 5), center=(0, 0, 0), up=(0, 1, 0), fovy=40, width=16, height=16),
+                         ambience=(0.5, 0.5, 0.5))
+        host = rt.HostScene(d, lib)
+        assert _blob_sections(sim.flatten(host))["root_is_leaf"] == 1
+        r = sim.render(host)
+        assert set(np.unique(r["hit_id"])) <= {-1, 0, 1} and (r["hit_id"] >= 0).any()
+
+
+def test_tile_sharding_partitions_the_image(rt, lib, sim):
+    """The union over ranks of the tile-sharded renders is the full image, each pixel written once."""
+    host = rt.HostScene(rt.scenes.mixed_small(width=70, height=45), lib)     # not multiples of 8x4
+    blob = sim.flatten(host)
+    full = sim.render(host, blob)
+    for world, chunk in ((2, 1), (3, 2), (8, 4)):
+        acc = np.zeros_like(full["rgba8"]); seen = np.zeros(full["hit_id"].shape, int)
+        for r in range(world):
+            part = sim.render(host, blob, tile=(r, world, chunk))
+            mask = part["hit_id"] != -2
+            seen += mask
+            acc[mask] = part["rgba8"][mask]
+        assert (seen == 1).all()
+        assert np.array_equal(acc, full["rgba8"])

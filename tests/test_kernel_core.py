@@ -1,0 +1,135 @@
+"""The kernel core (rt_core.cuh / rt_intersect.cuh) compiled for the host, against the oracle (CPU).
+Catches logic errors before GPU minutes are spent; the GPU parity tests proper are in test_gpu_parity.py."""
+import ast
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+SCENES = ["mixed_small", "spheres", "office", "rings", "molecule", "textured"]
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_core_matches_golden(rt, lib, sim, name):
+    g = np.load(os.path.join(GOLDEN, f"scene_{name}.npz"))
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**ast.literal_eval(str(g["kwargs"]))), lib)
+    r = sim.render(host)
+    assert np.array_equal(r["hit_id"], g["ids"])                      # bit-exact primitive ids
+    assert np.array_equal(r["hit_t"], g["t"])                         # bit-exact ray parameters
+    d = np.abs(r["rgba8"][..., :3].astype(int) - g["rgb8"].astype(int))
+    assert d.max() <= 1 and (d == 0).mean() >= 0.999
+    assert np.abs(r["pixels"][..., :3] - g["rgb"]).max() < 1e-6      # FP32 texels bound the colour error
+    c = r["counters"]
+    assert [c["rays_primary"], c["rays_shadow"], c["rays_reflect"]] == list(g["rays"])
+    assert (r["rgba8"][..., 3] == 255).all()
+
+
+def test_filter_never_changes_the_result(rt, lib, sim):
+    """FP32 filter + FP64 decide == FP64 everywhere (RT_FLAG_EXACT_ONLY), and the filter does filter."""
+    host = rt.HostScene(rt.scenes.office(width=96, height=54), lib)
+    blob = sim.flatten(host)
+    a = sim.render(host, blob)
+    b = sim.render(host, blob, flags=1)
+    for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+        assert np.array_equal(a[k], b[k])
+    assert a["counters"]["tri_exact"] < 0.15 * a["counters"]["tri_filter"]
+    assert b["counters"]["tri_exact"] == b["counters"]["tri_filter"]
+
+
+def test_supersampling_grid(rt, lib, sim):
+    g = np.load(os.path.join(GOLDEN, "scene_mixed_small_spp2.npz"))
+    host = rt.HostScene(rt.scenes.mixed_small(width=64, height=48), lib)
+    r = sim.render(host, spp_grid=2, want_ids=False)
+    assert np.abs(r["pixels"][..., :3] - g["rgb"]).max() < 1e-6
+    assert np.abs(r["rgba8"][..., :3].astype(int) - g["rgb8"].astype(int)).max() <= 1
+
+
+def test_tri_filter_is_conservative(sim, orc, oracle_kind):
+    """Property: whenever the reference test accepts a triangle with t <= thi, the FP32 filter passes it.
+    Adversarial mix: tiny far triangles, grazing rays, hits on edges/vertices, large coordinates."""
+    rng = np.random.default_rng(11)
+    accepted = passed_miss = misses = 0
+    for i in range(6000):
+        scale = 10.0 ** rng.uniform(-4, 1)
+        centre = rng.uniform(-1, 1, 3) * 10.0 ** rng.uniform(-1, 2.5)
+        p = centre + rng.normal(size=(3, 3)) * scale
+        dist = scale * 10.0 ** rng.uniform(0, 4)
+        mode = i % 4
+        if mode == 0:
+            w = rng.dirichlet((1, 1, 1))
+        elif mode == 1:                                   # on an edge / vertex
+            w = np.array([rng.random(), 0.0, 0.0]); w[1] = 1.0 - w[0]
+            w = np.roll(w, rng.integers(0, 3))
+        elif mode == 2:                                   # just outside an edge
+            w = rng.dirichlet((1, 1, 1)); w[rng.integers(0, 3)] = -10.0 ** rng.uniform(-9, -3); w /= w.sum()
+        else:
+            w = rng.uniform(-0.5, 1.5, 3); w /= w.sum()
+        target = w @ p
+        n = np.cross(p[1] - p[0], p[2] - p[0]); n /= np.linalg.norm(n) + 1e-300
+        dirn = rng.normal(size=3)
+        if i % 5 == 0:                                    # grazing
+            dirn = dirn - (dirn @ n) * n * (1.0 - 10.0 ** rng.uniform(-5, -1))
+        dirn /= np.linalg.norm(dirn)
+        o = target - dist * dirn
+        hit, out = orc.tri_test(p[0], p[1], p[2], o, dirn, kind=oracle_kind)
+        sh, sout = sim.tri_exact(p[0], p[1], p[2], o, dirn)
+        assert sh == hit and (not hit or sout[0] == out[0])          # exact stage == reference, bit for bit
+        if hit:
+            accepted += 1
+            assert sim.tri_filter(p[0], p[1], p[2], o, dirn, out[0]), (i, p, o, dirn)       # thi == t (tie)
+            assert sim.tri_filter(p[0], p[1], p[2], o, dirn, 1e300)
+        elif mode == 3 and dist < 100 * scale and np.abs(centre).max() < 100 * scale:
+            # well-conditioned clear misses: here the filter must actually reject
+            misses += 1
+            passed_miss += sim.tri_filter(p[0], p[1], p[2], o, dirn, 1e300)
+    assert accepted > 1500
+    assert misses > 100 and passed_miss < 0.25 * misses   # and it is a useful filter, not a pass-through
+
+
+def test_box_test_is_conservative(sim, orc, oracle_kind):
+    """Property: whenever the reference slab test accepts a box, the FP32 test on the outward-rounded box
+    does too (for thi = +inf), including axis-parallel rays and flat boxes."""
+    rng = np.random.default_rng(5)
+    n_acc = 0
+    for i in range(6000):
+        s = 10.0 ** rng.uniform(-3, 2)
+        mn = rng.uniform(-1, 1, 3) * s * 10
+        mx = mn + rng.uniform(0, 1, 3) * s
+        if i % 6 == 0:
+            k = rng.integers(0, 3); mx[k] = mn[k]
+        o = rng.uniform(-1, 1, 3) * s * 30
+        tgt = mn + (mx - mn) * rng.uniform(-0.2, 1.2, 3)
+        d = tgt - o
+        if i % 5 == 0:
+            d[rng.integers(0, 3)] = 0.0
+        if i % 11 == 0:
+            d[rng.integers(0, 3)] *= 1e-12
+        if not d.any():
+            continue
+        d /= np.linalg.norm(d)
+        hit, _ = orc.aabb_test(mn, mx, o, d, kind=oracle_kind)
+        if hit:
+            n_acc += 1
+            assert sim.box_test(mn, mx, o, d, 1e300), (i, mn, mx, o, d)
+    assert n_acc > 1500
+
+
+def test_tie_break_is_visit_order_independent(rt, lib, sim, orc, oracle_kind):
+    """Coplanar duplicated triangles: the lower BVH-order index must win, as in the reference's
+    left-first DFS with strict '<' (mybvh.cpp:169)."""
+    pos = np.array([[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0.0]])
+    quad = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    idx = np.concatenate([quad] * 6, 0)                   # 6 exact copies of the same two triangles
+    shift = np.concatenate([pos + np.array([3.0 * k, 0, 0]) for k in range(4)], 0)
+    idx2 = np.concatenate([quad + 4 * k for k in range(4)] * 3, 0)
+    for p, ix in ((pos, idx), (shift, idx2)):
+        desc = rt.SceneDesc("dups", [rt.MeshDesc(p, ix, rt.material((1, 1, 1), (1, 1, 1), (0, 0, 0), 1.0))], [],
+                            [((0, 0, 5), (1, 1, 1))],
+                            dict(eye=(p[:, 0].mean(), 0.3, 6), center=(p[:, 0].mean(), 0, 0), up=(0, 1, 0), fovy=60,
+                                 width=64, height=24))
+        host = rt.HostScene(desc, lib)
+        r = sim.render(host)
+        ref = orc.OracleScene(desc, oracle_kind).render()
+        assert np.array_equal(r["hit_id"], ref["ids"]) and (ref["ids"] >= 0).sum() > 40
