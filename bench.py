@@ -104,11 +104,11 @@ def cpu_leg(desc, seconds_target, kind_pref=("reference_fast", "reference", "por
     o = orc.OracleScene(desc, kind)
     H = int(desc.camera["height"])
     cores = os.cpu_count() or 1
-    probe = o.render(want_ids=False, y0=3, ystep=64)                     # ~1.6 % of the rows
+    probe = o.render(want_ids=False, y0=3, ystep=64, nthreads=cores)     # ~1.6 % of the rows
     rows_probe = len(range(3, H, 64))
     per_row = probe["seconds"] / rows_probe
     step = max(1, int(round(H * per_row / max(seconds_target, 1e-3))))
-    r = o.render(want_ids=False, y0=0, ystep=step)
+    r = o.render(want_ids=False, y0=0, ystep=step, nthreads=cores)   # torchrun exports OMP_NUM_THREADS=1
     rows = len(range(0, H, step))
     rays = sum(r["rays"].values())
     return {
@@ -190,7 +190,8 @@ def run_b200(args):
         bcast_ms = 0.0
     info = scene.info()
     cam = host.camera
-    tile = rdist.tile_share(rank, world) if world > 1 else (0, 1, 1)
+    chunk = int(os.environ.get("RT_TILE_CHUNK", "0")) or None
+    tile = rdist.tile_share(rank, world, chunk) if world > 1 else (0, 1, 1)
     params = host.params(tile=tile)
     d_lpos = torch.tensor(host.lights_pos, dtype=torch.float64, device=dev)
     d_lcol = torch.tensor(host.lights_color, dtype=torch.float64, device=dev)
@@ -279,11 +280,18 @@ def run_b200(args):
     L = nl
     flops = 24 * tot["box_tests"] + 48 * tot["tri_filter"] + (60 * L + 20) * tot["shaded_hits"]
     alg_bytes = 32 * tot["box_tests"] + 48 * tot["tri_filter"] + 64 * tot["shaded_hits"] + 16 * tot["texel_fetches"] + 4 * W * H
-    kms = sum(kern_ms) / len(kern_ms)
+    kms_local = sum(kern_ms) / len(kern_ms)
+    kms = kms_local
+    rank_ms = [kms_local]
     if world > 1:
-        kms = rdist.max_over_ranks(kms, dev)
+        kms = rdist.max_over_ranks(kms_local, dev)
+        g = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(g, torch.tensor([kms_local], dtype=torch.float64, device=dev))
+        rank_ms = [float(x.item()) for x in g]
+    peak_tflops *= world                                  # whole-job flops against the N-GPU peak
     achieved = flops / (kms * 1e-3) / 1e12
     roof = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
+            "kernel_ms_per_rank": rank_ms,
             "traffic": None, "kernel": "rtb::render_kernel<false>", "kernel_ms": kms,
             "peak_source": "148 SMs x 128 FP32 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json (FP32 is not in the "
                            "driver-measured set; the scene is L2-resident so HBM does not bound it)",
@@ -319,8 +327,26 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def _json_only_stdout():
+    """Libraries (NCCL's version banner, OpenMP/torchrun notices) write to fd 1; the contract is ONE JSON
+    line on stdout.  Point fd 1 at stderr for the whole run and keep the real stdout for the result."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
     a = parse()
+    _real_stdout = _json_only_stdout()
+    import builtins
+    _print = builtins.print
+
+    def _result_print(*args, **kw):          # the only print() calls in this file emit the JSON line
+        kw.setdefault("file", _real_stdout)
+        kw.setdefault("flush", True)
+        _print(*args, **kw)
+    print = _result_print                     # noqa: A001
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -150,7 +150,7 @@ def load_library(path: str | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("RT_B200_LIB") or LIB_PATH   # RT_B200_LIB: kernel-variant experiments only
     if not os.path.exists(p):
         raise RuntimeError(
             f"{p} not found: the CUDA extension is not built (run `python -c 'import __graft_entry__ as g; "

@@ -52,6 +52,8 @@ struct rt_scene {
   int32_t *d_ids = nullptr;
   double *d_t = nullptr;
   size_t cap_rgba8 = 0, cap_pixels = 0, cap_ids = 0, cap_t = 0;
+  double *d_scratch_d = nullptr; // cold per-lane state columns (RT_COLD == 2 builds)
+  int *d_scratch_i = nullptr;
   int *d_list = nullptr; // supersampling pixel list
   size_t cap_list = 0;
   int grid_plain = 0, grid_count = 0;
@@ -135,6 +137,11 @@ int adopt_blob(rt_scene *s) {
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, render_kernel<true>, kBlockThreads, 0));
   s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
   s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
+  {
+    const size_t threads = (size_t)(s->grid_plain > s->grid_count ? s->grid_plain : s->grid_count) * kBlockThreads;
+    RT_CUDA(cudaMalloc(&s->d_scratch_d, threads * CD_NUM * sizeof(double)));
+    RT_CUDA(cudaMalloc(&s->d_scratch_i, threads * CI_NUM * sizeof(int)));
+  }
   std::memset(&s->info, 0, sizeof(s->info));
   s->info.num_triangles = h.num_tris; s->info.num_meshes = h.num_meshes; s->info.num_objects = h.num_objects;
   s->info.num_nodes_ref = h.num_nodes_ref; s->info.num_nodes_flat = h.num_nodes;
@@ -153,6 +160,8 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   a.list_count_ptr = d_list_count;
   a.work_counter = s->d_work;
   a.counters = s->d_counters;
+  a.scratch_d = s->d_scratch_d;
+  a.scratch_i = s->d_scratch_i;
   const bool count = (fp.flags & RT_FLAG_COUNTERS) != 0;
   RT_CUDA(cudaMemsetAsync(s->d_work, 0, sizeof(unsigned long long), st));
   if (count) RT_CUDA(cudaMemsetAsync(s->d_counters, 0, sizeof(unsigned long long) * C_COUNT, st));
@@ -248,7 +257,7 @@ int rt_scene_destroy(rt_scene *s) {
   for (cudaTextureObject_t t : s->tex) if (t) cudaDestroyTextureObject(t);
   auto F = [](void *p) { if (p) cudaFree(p); };
   F(s->d_blob); F(s->d_tex); F(s->d_work); F(s->d_counters); F(s->d_lights);
-  F(s->d_rgba8); F(s->d_pixels); F(s->d_ids); F(s->d_t); F(s->d_list);
+  F(s->d_scratch_d); F(s->d_scratch_i); F(s->d_rgba8); F(s->d_pixels); F(s->d_ids); F(s->d_t); F(s->d_list);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
   if (s->stream) cudaStreamDestroy(s->stream);

@@ -9,7 +9,12 @@
 //   * recursion -> loop state (depth, accumulated weight), as the north star asks;
 //   * shadow rays terminate on the first confirmed occluder (any-hit);
 //   * bounces stop when mirror == 0 (CPU semantics, mytracer.cpp:547), unlike the reference
-//     kernel that always runs max_depth bounces.
+//     kernel that always runs max_depth bounces;
+//   * HOT / COLD state split: the traversal loop keeps only FP32 ray constants and a few ints in
+//     registers (struct Hot); everything FP64 — the exact ray, the best distance, the hit point,
+//     normal, colours, weights (struct Cold, 29 doubles + 6 ints = 256 B per lane) — lives in
+//     shared memory, one column per thread.  That halves the register count of the v1 kernel
+//     (168 -> ~80) and doubles the resident warps (profiles/r01_ncu_render_kernel_v1.md).
 // The same code is compiled for the device and — for tests only — for the host.
 #ifndef RTB_CORE_CUH
 #define RTB_CORE_CUH
@@ -32,27 +37,36 @@ struct Ctx {
   unsigned int *cnt;     // per-thread counters (COUNT builds) or nullptr
 };
 
-struct Lane {
-  // --- ray in flight -------------------------------------------------------------------
-  D3 o, d;
+// ---- cold per-lane state: shared memory columns on the device, a plain array on the host ----------
+enum ColdD { // double slots
+  CD_O = 0, CD_D = 3, CD_BEST_T = 6, CD_P = 7, CD_N = 10, CD_V = 13, CD_KD = 16, CD_L = 19, CD_COL = 22,
+  CD_ACC = 25, CD_WEIGHT = 28, CD_NUM = 29
+};
+enum ColdI { CI_PX = 0, CI_PY, CI_SAMPLE, CI_DEPTH, CI_MAT, CI_LIGHT, CI_NUM };
+constexpr int kColdBytesPerLane = CD_NUM * 8 + CI_NUM * 4; // 256
+
+template <int STRIDE> struct Cold {
+  double *db; // &doubles[lane]
+  int *ib;    // &ints[lane]
+  long long rstride; // used when STRIDE == 0 (runtime stride: global scratch columns)
+  RT_HD long long st() const { return STRIDE ? (long long)STRIDE : rstride; }
+  RT_HD double &d(int k) const { return db[k * st()]; }
+  RT_HD int &i(int k) const { return ib[k * st()]; }
+  RT_HD D3 v(int k) const { return mk(db[k * st()], db[(k + 1) * st()], db[(k + 2) * st()]); }
+  RT_HD void set(int k, const D3 &a) const {
+    db[k * st()] = a.x; db[(k + 1) * st()] = a.y; db[(k + 2) * st()] = a.z;
+  }
+};
+
+// ---- hot per-lane state (registers) -------------------------------------------------------------------
+struct Hot {
   RayF rf;
-  double best_t; // nearest: best distance so far; any-hit: light distance (exclusive bound)
-  float thi;     // FP32 upper bound of best_t used for culling
+  float thi;   // FP32 upper bound of the best distance, used for culling
   int best_id;
-  int node;      // >= 0: interior NodeRec to visit next; < 0: traversal finished
+  int node;    // >= 0: interior NodeRec to visit next; < 0: traversal finished
   int sp;
   int mode;
-  int found;     // any-hit result
-  // --- path ------------------------------------------------------------------------------
-  int px, py;
-  int sample, depth;
-  double weight;
-  D3 col, acc;
-  // --- hit being shaded ---------------------------------------------------------------
-  D3 P, N, V;
-  D3 kd, L;
-  int mat;       // >= 0: mesh index; < 0: ~object index
-  int light_k;
+  int found;   // any-hit result
 };
 
 struct Mat {
@@ -60,6 +74,43 @@ struct Mat {
   double shininess, mirror;
   int shadowable;
 };
+
+#ifndef RT_LDG
+#define RT_LDG 1
+#endif
+struct F4 {
+  float x, y, z, w;
+};
+struct I4 {
+  int x, y, z, w;
+};
+// 16-byte read-only loads ("vectorised __ldg", north star (a))
+RT_HD F4 ld_f4(const void *p) {
+#if defined(__CUDA_ARCH__)
+#if RT_LDG
+  const float4 v = __ldg(reinterpret_cast<const float4 *>(p));
+#else
+  const float4 v = *reinterpret_cast<const float4 *>(p);
+#endif
+  F4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+  return r;
+#else
+  return *reinterpret_cast<const F4 *>(p);
+#endif
+}
+RT_HD I4 ld_i4(const void *p) {
+#if defined(__CUDA_ARCH__)
+#if RT_LDG
+  const int4 v = __ldg(reinterpret_cast<const int4 *>(p));
+#else
+  const int4 v = *reinterpret_cast<const int4 *>(p);
+#endif
+  I4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+  return r;
+#else
+  return *reinterpret_cast<const I4 *>(p);
+#endif
+}
 
 template <bool COUNT> RT_HD void bump(const Ctx &c, int which, unsigned n = 1) {
   if (COUNT) c.cnt[which] += n;
@@ -89,113 +140,152 @@ RT_HD D3 fetch_texel(const SceneView &sv, int mesh, const MeshRec &mr, int px, i
 #endif
 }
 
+RT_HD float thi_of(double t) { return fminf(f_up(t) * (1.0f + 8.0f * kU32), FLT_MAX); }
+
 // ---------------------------------------------------------------------------------------
 // ray start: Ray(origin, dir) normalises dir (oracle/shim/utils/Ray.h), then the analytic
 // primitives are tested in list order (restated intersect_scene), then the BVH is entered.
 // ---------------------------------------------------------------------------------------
-template <bool COUNT>
-RT_HD void start_ray(const Ctx &c, Lane &L, const D3 &origin, const D3 &dir, int mode, double tmax) {
-  L.o = origin;
-  L.d = normalize(dir);
-  rayf_setup(L.rf, L.o, L.d);
-  L.mode = mode;
-  L.best_t = tmax;
-  L.best_id = -1;
-  L.found = 0;
-  L.sp = 0;
+template <bool COUNT, int S>
+RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, const D3 &dir, int mode, double tmax) {
+  const D3 o = origin;
+  const D3 d = normalize(dir);
+  C.set(CD_O, o);
+  C.set(CD_D, d);
+  rayf_setup(H.rf, o, d);
+  H.mode = mode;
+  H.best_id = -1;
+  H.found = 0;
+  H.sp = 0;
+  double best = tmax;
   const SceneView &sv = c.sv;
   for (int k = 0; k < sv.num_objects; ++k) {
     const ObjectRec &ob = sv.objects[k];
     double t;
     bump<COUNT>(c, C_OBJECT);
-    const bool hit = (ob.kind == 0) ? sphere_exact(L.o, L.d, ld3(ob.center), ob.radius, t)
-                                    : plane_exact(L.o, L.d, ld3(ob.center), ld3(ob.normal), t);
-    if (hit && t < L.best_t) {
-      if (mode == M_ANYHIT) { L.found = 1; L.node = -1; return; }
-      L.best_t = t;
-      L.best_id = sv.num_tris + k;
+    const bool hit = (ob.kind == 0) ? sphere_exact(o, d, ld3(ob.center), ob.radius, t)
+                                    : plane_exact(o, d, ld3(ob.center), ld3(ob.normal), t);
+    if (hit && t < best) {
+      if (mode == M_ANYHIT) { H.found = 1; H.node = -1; C.d(CD_BEST_T) = best; return; }
+      best = t;
+      H.best_id = sv.num_tris + k;
     }
   }
-  const float up = f_up(L.best_t);
-  L.thi = fminf(up * (1.0f + 8.0f * kU32), FLT_MAX);
-  L.node = (sv.num_nodes > 0) ? 0 : -1;
+  C.d(CD_BEST_T) = best;
+  H.thi = thi_of(best);
+  H.node = (sv.num_nodes > 0) ? 0 : -1;
 }
 
-template <bool COUNT> RT_HD void leaf_test(const Ctx &c, Lane &L, int first, int count) {
-  const SceneView &sv = c.sv;
+// FP64 confirmation of one filter survivor + nearest / any-hit bookkeeping.  Rare (~0.7 per ray).
+template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const Cold<S> &C, int i) {
+  bump<COUNT>(c, C_TRI_EXACT);
+  const TriExact &e = c.sv.exact[i];
+  TriHit h;
+  if (!tri_exact(C.v(CD_O), C.v(CD_D), ld3(e.p0), ld3(e.p1), ld3(e.p2), h)) return;
+  const double best = C.d(CD_BEST_T);
+  if (H.mode == M_ANYHIT) {
+    // isShadow = hit && t < light_distance && 0 < t   (mytracer.cpp:599)
+    if (h.t < best) { H.found = 1; H.node = -1; }
+    return;
+  }
+  // strict '<' keeps the first hit in DFS order (mybvh.cpp:169); leaves are visited in ascending
+  // triangle index there, so "lower index wins a tie" is visit-order independent.  Analytic
+  // primitives are tested before the BVH, so they win ties against triangles.
+  const bool better = (h.t < best) || (h.t == best && H.best_id >= 0 && H.best_id < c.sv.num_tris && i < H.best_id);
+  if (better) {
+    C.d(CD_BEST_T) = h.t;
+    H.best_id = i;
+    H.thi = thi_of(h.t);
+  }
+}
+
+template <bool COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int count) {
   const bool exact_only = (c.fp.flags & 1) != 0;
   for (int i = first; i < first + count; ++i) {
     bump<COUNT>(c, C_TRI_FILTER);
+    bool pass = exact_only;
     if (!exact_only) {
-      const TriFilter f = sv.filt[i];
-      if (!tri_filter(L.rf, f, L.thi)) continue;
+      const char *p = reinterpret_cast<const char *>(c.sv.filt + i);
+      const F4 a = ld_f4(p), b = ld_f4(p + 16), d = ld_f4(p + 32);
+      TriFilter f;
+      f.p2[0] = a.x; f.p2[1] = a.y; f.p2[2] = a.z; f.k_bary = a.w;
+      f.e1[0] = b.x; f.e1[1] = b.y; f.e1[2] = b.z; f.k_t = b.w;
+      f.e2[0] = d.x; f.e2[1] = d.y; f.e2[2] = d.z; f.k_det = d.w;
+      pass = tri_filter(H.rf, f, H.thi);
     }
-    bump<COUNT>(c, C_TRI_EXACT);
-    const TriExact &e = sv.exact[i];
-    TriHit h;
-    if (!tri_exact(L.o, L.d, ld3(e.p0), ld3(e.p1), ld3(e.p2), h)) continue;
-    if (L.mode == M_ANYHIT) {
-      // isShadow = hit && t < light_distance && 0 < t   (mytracer.cpp:599)
-      if (h.t < L.best_t) { L.found = 1; L.node = -1; return; }
-    } else {
-      // strict '<' keeps the first hit in DFS order (mybvh.cpp:169); leaves are visited in
-      // ascending triangle index there, so "lower index wins a tie" is visit-order independent.
-      // Analytic primitives are tested before the BVH, so they win ties against triangles.
-      const bool better = (h.t < L.best_t) || (h.t == L.best_t && L.best_id >= 0 &&
-                                               L.best_id < sv.num_tris && i < L.best_id);
-      if (better) {
-        L.best_t = h.t;
-        L.best_id = i;
-        L.thi = fminf(f_up(h.t) * (1.0f + 8.0f * kU32), FLT_MAX);
-      }
+    if (pass) {
+      confirm_tri<COUNT>(c, H, C, i);
+      if (H.found) return;
     }
   }
 }
 
-// One traversal step: load one 64-byte node, test both child boxes, intersect leaf children,
-// descend into the nearer interior child (push the other) or pop.
-template <bool COUNT> RT_HD void trav_step(const Ctx &c, Lane &L, int *stk) {
-  const NodeRec n = c.sv.nodes[L.node];
+// One traversal step: one 64-byte node record (four 16-byte read-only loads), two conservative
+// slab tests, leaf children intersected at once, nearer interior child next, the other pushed
+// together with its entry distance so that stale entries are culled when popped.
+// The kernel calls this from a WARP-UNIFORM loop (while (__any_sync(node >= 0)) if (node >= 0) step):
+// the vote re-converges the warp every iteration.  A per-lane `while (node >= 0)` loop lets lanes
+// drift out of phase and ran 2x slower on B200 (profiles/r01_variants.md).
+template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, int *stk) {
+  const char *np = reinterpret_cast<const char *>(c.sv.nodes) + (size_t)(unsigned)H.node * 64u;
+  const F4 q0 = ld_f4(np), q1 = ld_f4(np + 16), q2 = ld_f4(np + 32);
+  const I4 r = ld_i4(np + 48);
   bump<COUNT>(c, C_NODES);
   bump<COUNT>(c, C_BOX, 2);
+  // q0 = c0.min.xyz c0.max.x | q1 = c0.max.yz c1.min.xy | q2 = c1.min.z c1.max.xyz
+  const float b0mn[3] = {q0.x, q0.y, q0.z}, b0mx[3] = {q0.w, q1.x, q1.y};
+  const float b1mn[3] = {q1.z, q1.w, q2.x}, b1mx[3] = {q2.y, q2.z, q2.w};
   float tn0, tn1;
-  bool h0 = box_test(L.rf, n.c0_min, n.c0_max, L.thi, tn0);
-  bool h1 = box_test(L.rf, n.c1_min, n.c1_max, L.thi, tn1);
-  if (h0 && n.cnt0 > 0) {
-    leaf_test<COUNT>(c, L, n.ref0, n.cnt0);
+  bool h0 = box_test(H.rf, b0mn, b0mx, H.thi, tn0);
+  bool h1 = box_test(H.rf, b1mn, b1mx, H.thi, tn1);
+  if (h0 && r.z > 0) {
+    leaf_test<COUNT>(c, H, C, r.x, r.z);
     h0 = false;
-    if (L.found) return;
   }
-  if (h1 && n.cnt1 > 0) {
-    leaf_test<COUNT>(c, L, n.ref1, n.cnt1);
+  if (h1 && r.w > 0 && !H.found) {
+    leaf_test<COUNT>(c, H, C, r.y, r.w);
     h1 = false;
-    if (L.found) return;
   }
-  int next;
+  if (H.found) { H.node = -1; return; }
+  int node, sp = H.sp;
   if (h0 && h1) {
     const bool far0 = tn1 < tn0;
-    next = far0 ? n.ref1 : n.ref0;
-    stk[L.sp++] = far0 ? n.ref0 : n.ref1;
+    stk[2 * sp] = far0 ? r.x : r.y;
+    stk[2 * sp + 1] = __float_as_int_rt(far0 ? tn0 : tn1);
+    ++sp;
+    node = far0 ? r.y : r.x;
   } else if (h0) {
-    next = n.ref0;
+    node = r.x;
   } else if (h1) {
-    next = n.ref1;
+    node = r.y;
   } else {
-    next = (L.sp > 0) ? stk[--L.sp] : -1;
+    node = -1;
+    while (sp > 0) {
+      --sp;
+      const float tn = __int_as_float_rt(stk[2 * sp + 1]);
+      if (tn <= H.thi) { node = stk[2 * sp]; break; } // else: culled, a nearer hit was found meanwhile
+    }
   }
-  L.node = next;
+  H.node = node;
+  H.sp = sp;
+}
+
+// host/test build: run this lane's ray to completion
+template <bool COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, int *stk) {
+  while (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
 }
 
 // ---------------------------------------------------------------------------------------
-// path logic
+// path logic (cold: FP64, runs once per ray, not per node)
 // ---------------------------------------------------------------------------------------
-template <bool COUNT> RT_HD void start_primary(const Ctx &c, Lane &L) {
+template <bool COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const Cold<S> &C) {
   const CameraRec &cam = c.fp.cam;
-  double x = (double)L.px, y = (double)L.py;
+  double x = (double)C.i(CI_PX), y = (double)C.i(CI_PY);
   const int s = c.fp.spp_grid;
   if (s > 1) {
     // sub-pixel grid, offsets as mytracer_gpu.cu:203-207: si/s - 0.5 + 1/(2s)
-    const int si = L.sample / s, sj = L.sample % s;
+    const int sample = C.i(CI_SAMPLE);
+    const int si = sample / s, sj = sample % s;
     const double xo = dadd(dsub(ddiv((double)si, (double)s), 0.5), ddiv(1.0, dmul(2.0, (double)s)));
     const double yo = dadd(dsub(ddiv((double)sj, (double)s), 0.5), ddiv(1.0, dmul(2.0, (double)s)));
     x = dadd(x, xo);
@@ -204,19 +294,19 @@ template <bool COUNT> RT_HD void start_primary(const Ctx &c, Lane &L) {
   // Camera::primary_ray: Ray(eye, lower_left + x*x_dir + y*y_dir - eye)
   const D3 eye = ld3(cam.eye);
   const D3 dir = sub(add(add(ld3(cam.lower_left), scale(x, ld3(cam.x_dir))), scale(y, ld3(cam.y_dir))), eye);
-  L.depth = 0;
-  L.weight = 1.0;
-  L.col = mk(0.0, 0.0, 0.0);
+  C.i(CI_DEPTH) = 0;
+  C.d(CD_WEIGHT) = 1.0;
+  C.set(CD_COL, mk(0.0, 0.0, 0.0));
   bump<COUNT>(c, C_RAY_PRIMARY);
-  start_ray<COUNT>(c, L, eye, dir, M_NEAREST, DBL_MAX);
+  start_ray<COUNT>(c, H, C, eye, dir, M_NEAREST, DBL_MAX);
 }
 
-RT_HD void write_pixel(const Ctx &c, Lane &L) {
-  D3 col = L.acc;
+template <int S> RT_HD void write_pixel(const Ctx &c, const Cold<S> &C) {
+  D3 col = C.v(CD_ACC);
   const int s2 = c.fp.spp_grid * c.fp.spp_grid;
   if (s2 > 1) col = divs(col, (double)s2);
   col = mk(dmin1(col.x), dmin1(col.y), dmin1(col.z)); // min(color, vec4(1,1,1)) mytracer_gpu.cu:155
-  const size_t p = (size_t)L.py * (size_t)c.fp.cam.width + (size_t)L.px;
+  const size_t p = (size_t)C.i(CI_PY) * (size_t)c.fp.cam.width + (size_t)C.i(CI_PX);
   if (c.out.pixels) {
     double *q = c.out.pixels + 4 * p;
     q[0] = col.x; q[1] = col.y; q[2] = col.z; q[3] = 0.0;
@@ -232,33 +322,38 @@ RT_HD void write_pixel(const Ctx &c, Lane &L) {
   }
 }
 
-template <bool COUNT> RT_HD void sample_done(const Ctx &c, Lane &L) {
-  L.acc = add(L.acc, L.col);
-  L.sample++;
-  if (L.sample < c.fp.spp_grid * c.fp.spp_grid) {
-    start_primary<COUNT>(c, L);
+template <bool COUNT, int S> RT_HD void sample_done(const Ctx &c, Hot &H, const Cold<S> &C) {
+  C.set(CD_ACC, add(C.v(CD_ACC), C.v(CD_COL)));
+  const int sample = C.i(CI_SAMPLE) + 1;
+  C.i(CI_SAMPLE) = sample;
+  if (sample < c.fp.spp_grid * c.fp.spp_grid) {
+    start_primary<COUNT>(c, H, C);
   } else {
-    write_pixel(c, L);
-    L.mode = M_IDLE;
-    L.node = -1;
+    write_pixel(c, C);
+    H.mode = M_IDLE;
+    H.node = -1;
   }
 }
 
-// Fill P, N, kd, mat for the nearest hit and start the lighting loop (L = ambient term).
-template <bool COUNT> RT_HD void hit_setup(const Ctx &c, Lane &L) {
+// Fill P, N, V, kd, mat for the nearest hit and start the lighting loop (L = ambient term).
+template <bool COUNT, int S> RT_HD void hit_setup(const Ctx &c, Hot &H, const Cold<S> &C, Mat &m) {
   const SceneView &sv = c.sv;
-  L.V = neg(L.d);
-  if (L.best_id < sv.num_tris) {
-    const int i = L.best_id;
+  const D3 o = C.v(CD_O), d = C.v(CD_D);
+  const double best = C.d(CD_BEST_T);
+  C.set(CD_V, neg(d));
+  D3 P, N, kd;
+  int mat;
+  if (H.best_id < sv.num_tris) {
+    const int i = H.best_id;
     const TriExact &e = sv.exact[i];
     TriHit h;
-    h.t = L.best_t; h.alpha = 0.0; h.beta = 0.0; h.gamma = 0.0;
-    tri_exact(L.o, L.d, ld3(e.p0), ld3(e.p1), ld3(e.p2), h); // same arithmetic as the accepted test
+    h.t = best; h.alpha = 0.0; h.beta = 0.0; h.gamma = 0.0;
+    tri_exact(o, d, ld3(e.p0), ld3(e.p1), ld3(e.p2), h); // same arithmetic as the accepted test
     const TriShade &s = sv.shade[i];
     const MeshRec &mr = sv.meshes[s.mesh];
-    L.mat = s.mesh;
-    L.P = along(L.o, h.t, L.d);                               // ray(t), mymesh.cpp:219
-    L.kd = ld3(mr.diffuse);
+    mat = s.mesh;
+    P = along(o, h.t, d);                                   // ray(t), mymesh.cpp:219
+    kd = ld3(mr.diffuse);
     if (mr.tex_w != -1) {
       // Mesh::compute_texture, mymesh.cpp:70-95
       double u = dadd(dadd(dmul(h.alpha, s.uv[0]), dmul(h.beta, s.uv[2])), dmul(h.gamma, s.uv[4]));
@@ -267,108 +362,121 @@ template <bool COUNT> RT_HD void hit_setup(const Ctx &c, Lane &L) {
       v = (v < 0.0) ? 0.0 : ((1.0 < v) ? 1.0 : v);
       const int tx = (int)round(dmul(u, (double)(unsigned)(mr.tex_w - 1)));
       const int ty = (int)round(dmul(dsub(1.0, v), (double)(unsigned)(mr.tex_h - 1)));
-      L.kd = fetch_texel(sv, s.mesh, mr, tx, ty);
+      kd = fetch_texel(sv, s.mesh, mr, tx, ty);
       bump<COUNT>(c, C_TEXEL);
     }
     if (mr.draw_mode == 0) {
-      L.N = ld3(s.n);                                          // stored face normal, mymesh.cpp:228-229
+      N = ld3(s.n);                                          // stored face normal, mymesh.cpp:228-229
     } else {
       // alpha*n0 + beta*n1 + gamma*n2, NOT re-normalised (mymesh.cpp:231-233)
-      L.N = add(add(scale(h.alpha, ld3(s.n)), scale(h.beta, ld3(s.n + 3))), scale(h.gamma, ld3(s.n + 6)));
+      N = add(add(scale(h.alpha, ld3(s.n)), scale(h.beta, ld3(s.n + 3))), scale(h.gamma, ld3(s.n + 6)));
     }
   } else {
-    const int k = L.best_id - sv.num_tris;
+    const int k = H.best_id - sv.num_tris;
     const ObjectRec &ob = sv.objects[k];
-    L.mat = ~k;
-    L.P = along(L.o, L.best_t, L.d);
-    L.kd = ld3(ob.diffuse);
-    L.N = (ob.kind == 0) ? divs(sub(L.P, ld3(ob.center)), ob.radius) : ld3(ob.normal);
+    mat = ~k;
+    P = along(o, best, d);
+    kd = ld3(ob.diffuse);
+    N = (ob.kind == 0) ? divs(sub(P, ld3(ob.center)), ob.radius) : ld3(ob.normal);
   }
-  Mat m;
-  load_mat(sv, L.mat, m);
+  C.set(CD_P, P);
+  C.set(CD_N, N);
+  C.set(CD_KD, kd);
+  C.i(CI_MAT) = mat;
+  load_mat(sv, mat, m);
   // ambient term, mytracer.cpp:574-576
-  L.L = mk(dadd(0.0, dmul(c.fp.ambience[0], m.ka.x)), dadd(0.0, dmul(c.fp.ambience[1], m.ka.y)),
-           dadd(0.0, dmul(c.fp.ambience[2], m.ka.z)));
-  L.light_k = 0;
+  C.set(CD_L, mk(dadd(0.0, dmul(c.fp.ambience[0], m.ka.x)), dadd(0.0, dmul(c.fp.ambience[1], m.ka.y)),
+                 dadd(0.0, dmul(c.fp.ambience[2], m.ka.z))));
+  C.i(CI_LIGHT) = 0;
   bump<COUNT>(c, C_SHADED);
 }
 
 // diffuse + specular of one unshadowed light, mytracer.cpp:510-534,581-585,603-605
-RT_HD void add_light(const Ctx &c, Lane &L, const Mat &m, int k) {
+template <int S> RT_HD void add_light(const Ctx &c, const Cold<S> &C, const Mat &m, int k) {
   const double *lcol = c.light_col + 4 * k;
-  const D3 lv = sub(ld3(c.light_pos + 4 * k), L.P);
+  const D3 P = C.v(CD_P), N = C.v(CD_N);
+  const D3 lv = sub(ld3(c.light_pos + 4 * k), P);
   const D3 l = normalize(lv);
-  const double diff = dmax0(dot(L.N, l));
+  const double diff = dmax0(dot(N, l));
   double refl = 0.0;
   if (diff > 0.0) {
-    const D3 r = normalize(mirror(l, L.N));
-    refl = dmax0(dot(r, L.V));
+    const D3 r = normalize(mirror(l, N));
+    refl = dmax0(dot(r, C.v(CD_V)));
   }
   const double spec = pow(refl, m.shininess);
-  L.L.x = dadd(L.L.x, dmul(lcol[0], dadd(dmul(L.kd.x, diff), dmul(m.ks.x, spec))));
-  L.L.y = dadd(L.L.y, dmul(lcol[1], dadd(dmul(L.kd.y, diff), dmul(m.ks.y, spec))));
-  L.L.z = dadd(L.L.z, dmul(lcol[2], dadd(dmul(L.kd.z, diff), dmul(m.ks.z, spec))));
+  const D3 kd = C.v(CD_KD);
+  D3 L = C.v(CD_L);
+  L.x = dadd(L.x, dmul(lcol[0], dadd(dmul(kd.x, diff), dmul(m.ks.x, spec))));
+  L.y = dadd(L.y, dmul(lcol[1], dadd(dmul(kd.y, diff), dmul(m.ks.y, spec))));
+  L.z = dadd(L.z, dmul(lcol[2], dadd(dmul(kd.z, diff), dmul(m.ks.z, spec))));
+  C.set(CD_L, L);
 }
 
 // Advance a lane whose traversal has finished until it has a new ray in flight or is idle.
-template <bool COUNT> RT_HD void advance(const Ctx &c, Lane &L) {
+template <bool COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<S> &C) {
   const SceneView &sv = c.sv;
-  while (L.mode != M_IDLE && L.node < 0) {
+  while (H.mode != M_IDLE && H.node < 0) {
     Mat m;
-    if (L.mode == M_NEAREST) {
-      if (L.depth == 0 && c.fp.spp_grid == 1) {
-        const size_t p = (size_t)L.py * (size_t)c.fp.cam.width + (size_t)L.px;
-        if (c.out.hit_id) c.out.hit_id[p] = L.best_id;
-        if (c.out.hit_t) c.out.hit_t[p] = (L.best_id >= 0) ? L.best_t : -1.0;
+    if (H.mode == M_NEAREST) {
+      if (C.i(CI_DEPTH) == 0 && c.fp.spp_grid == 1) {
+        const size_t p = (size_t)C.i(CI_PY) * (size_t)c.fp.cam.width + (size_t)C.i(CI_PX);
+        if (c.out.hit_id) c.out.hit_id[p] = H.best_id;
+        if (c.out.hit_t) c.out.hit_t[p] = (H.best_id >= 0) ? C.d(CD_BEST_T) : -1.0;
       }
-      if (L.best_id < 0) {
+      if (H.best_id < 0) {
         // miss: primary -> background; bounce -> weight * background (mytracer_gpu.cu:262,292)
-        L.col = add(L.col, scale(L.weight, ld3(c.fp.background)));
-        sample_done<COUNT>(c, L);
+        C.set(CD_COL, add(C.v(CD_COL), scale(C.d(CD_WEIGHT), ld3(c.fp.background))));
+        sample_done<COUNT>(c, H, C);
         continue;
       }
-      hit_setup<COUNT>(c, L);
-      load_mat(sv, L.mat, m);
-    } else { // M_ANYHIT finished: light_k was the light under test
-      load_mat(sv, L.mat, m);
-      if (!L.found) add_light(c, L, m, L.light_k);
-      L.light_k++;
+      hit_setup<COUNT>(c, H, C, m);
+    } else { // M_ANYHIT finished: CI_LIGHT was the light under test
+      load_mat(sv, C.i(CI_MAT), m);
+      if (!H.found) add_light(c, C, m, C.i(CI_LIGHT));
+      C.i(CI_LIGHT) = C.i(CI_LIGHT) + 1;
     }
-    L.mode = M_SHADE;
+    H.mode = M_SHADE;
     // lighting loop, mytracer.cpp:579-606
-    while (L.light_k < c.fp.num_lights) {
+    int k = C.i(CI_LIGHT);
+    while (k < c.fp.num_lights) {
       if (m.shadowable) {
-        const D3 lv = sub(ld3(c.light_pos + 4 * L.light_k), L.P);
+        const D3 P = C.v(CD_P);
+        const D3 lv = sub(ld3(c.light_pos + 4 * k), P);
         const D3 ldir = normalize(lv);
         const double ldist = norm(lv);
         bump<COUNT>(c, C_RAY_SHADOW);
-        start_ray<COUNT>(c, L, add(L.P, scale(1e-4, ldir)), ldir, M_ANYHIT, ldist);
+        start_ray<COUNT>(c, H, C, add(P, scale(1e-4, ldir)), ldir, M_ANYHIT, ldist);
         break;
       }
-      add_light(c, L, m, L.light_k);
-      L.light_k++;
+      add_light(c, C, m, k);
+      ++k;
     }
-    if (L.mode == M_ANYHIT) continue; // shadow ray in flight (or already resolved: node < 0)
+    C.i(CI_LIGHT) = k;
+    if (H.mode == M_ANYHIT) continue; // shadow ray in flight (or already resolved: node < 0)
     // all lights done: colour of this bounce, then the mirror bounce (mytracer.cpp:546-555)
-    L.col = add(L.col, scale(L.weight, scale(dsub(1.0, m.mirror), L.L)));
-    if (m.mirror > 0.0 && L.depth < c.fp.max_depth) {
-      const D3 v = reflect(neg(L.V), L.N);
-      L.weight = dmul(L.weight, m.mirror);
-      L.depth++;
+    const double w = C.d(CD_WEIGHT);
+    C.set(CD_COL, add(C.v(CD_COL), scale(w, scale(dsub(1.0, m.mirror), C.v(CD_L)))));
+    const int depth = C.i(CI_DEPTH);
+    if (m.mirror > 0.0 && depth < c.fp.max_depth) {
+      const D3 N = C.v(CD_N), P = C.v(CD_P);
+      const D3 v = reflect(neg(C.v(CD_V)), N);
+      C.d(CD_WEIGHT) = dmul(w, m.mirror);
+      C.i(CI_DEPTH) = depth + 1;
       bump<COUNT>(c, C_RAY_REFLECT);
-      start_ray<COUNT>(c, L, add(L.P, scale(1e-4, v)), v, M_NEAREST, DBL_MAX);
+      start_ray<COUNT>(c, H, C, add(P, scale(1e-4, v)), v, M_NEAREST, DBL_MAX);
     } else {
-      sample_done<COUNT>(c, L);
+      sample_done<COUNT>(c, H, C);
     }
   }
 }
 
 // Begin a pixel (lane must be idle).
-template <bool COUNT> RT_HD void begin_pixel(const Ctx &c, Lane &L, int px, int py) {
-  L.px = px; L.py = py;
-  L.sample = 0;
-  L.acc = mk(0.0, 0.0, 0.0);
-  start_primary<COUNT>(c, L);
+template <bool COUNT, int S> RT_HD void begin_pixel(const Ctx &c, Hot &H, const Cold<S> &C, int px, int py) {
+  C.i(CI_PX) = px;
+  C.i(CI_PY) = py;
+  C.i(CI_SAMPLE) = 0;
+  C.set(CD_ACC, mk(0.0, 0.0, 0.0));
+  start_primary<COUNT>(c, H, C);
 }
 
 // Map a work slot (owned tile j, lane l) to a pixel; false if it falls outside the image or

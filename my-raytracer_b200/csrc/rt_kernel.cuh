@@ -31,10 +31,18 @@ struct KernelArgs {
   const int *list_count_ptr;        // optional: list length produced on the device (no host sync)
   unsigned long long *work_counter; // zeroed before every launch
   unsigned long long *counters;     // C_COUNT entries (COUNT builds)
+  double *scratch_d;                // RT_COLD == 2: CD_NUM columns of grid*block doubles
+  int *scratch_i;                   //               CI_NUM columns of grid*block ints
 };
 
+#ifndef RT_COLD
+#define RT_COLD 0
+#endif
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 4
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlockThreads) render_kernel(const __grid_constant__ KernelArgs a) {
+__global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(const __grid_constant__ KernelArgs a) {
   unsigned int cnt[COUNT ? C_COUNT : 1];
   if (COUNT) {
 #pragma unroll
@@ -48,20 +56,42 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const __grid_cons
   c.list_count = a.list_count_ptr ? *a.list_count_ptr : a.list_count;
   c.cnt = cnt;
 
-  int stk[kStackMax];
-  Lane L;
-  L.mode = M_IDLE;
-  L.node = -1;
+  // cold per-lane state: one shared-memory column per thread (rt_core.cuh)
+#if RT_COLD == 0   // shared-memory columns
+  __shared__ double cold_d[CD_NUM * kBlockThreads];
+  __shared__ int cold_i[CI_NUM * kBlockThreads];
+  Cold<kBlockThreads> C;
+  C.db = cold_d + threadIdx.x;
+  C.ib = cold_i + threadIdx.x;
+#elif RT_COLD == 1 // registers / local memory (compiler's choice)
+  double cold_d[CD_NUM];
+  int cold_i[CI_NUM];
+  Cold<1> C;
+  C.db = cold_d;
+  C.ib = cold_i;
+#else              // global scratch columns
+  Cold<0> C;
+  C.rstride = (long long)gridDim.x * kBlockThreads;
+  C.db = a.scratch_d + (size_t)blockIdx.x * kBlockThreads + threadIdx.x;
+  C.ib = a.scratch_i + (size_t)blockIdx.x * kBlockThreads + threadIdx.x;
+#endif
+  int stk[2 * kStackMax];
+  Hot H;
+  H.mode = M_IDLE;
+  H.node = -1;
+  H.sp = 0;
+  H.found = 0;
+  H.best_id = -1;
   const long long slots = work_slots(c);
   const unsigned lane = threadIdx.x & 31u;
   bool exhausted = false; // warp-uniform
 
   while (true) {
-    // ---- phase A: path logic for lanes whose traversal finished ---------------------------
-    if (L.mode != M_IDLE && L.node < 0) advance<COUNT>(c, L);
+    // ---- phase A: path logic (FP64, cold state) for lanes whose traversal finished -----------
+    if (H.mode != M_IDLE && H.node < 0) advance<COUNT>(c, H, C);
 
     // ---- warp-level work fetch for idle lanes ----------------------------------------------
-    const unsigned idle = __ballot_sync(kFullMask, L.mode == M_IDLE);
+    const unsigned idle = __ballot_sync(kFullMask, H.mode == M_IDLE);
     if (idle != 0u && !exhausted) {
       const int n = __popc(idle);
       const int leader = __ffs(idle) - 1;
@@ -70,20 +100,20 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const __grid_cons
       base = __shfl_sync(kFullMask, base, leader);
       if ((long long)base >= slots) {
         exhausted = true;
-      } else if (L.mode == M_IDLE) {
+      } else if (H.mode == M_IDLE) {
         const long long mine = (long long)base + __popc(idle & ((1u << lane) - 1u));
         int px, py;
-        if (mine < slots && work_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, L, px, py);
+        if (mine < slots && work_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
       }
     }
-    const unsigned busy = __ballot_sync(kFullMask, L.mode != M_IDLE);
+    const unsigned busy = __ballot_sync(kFullMask, H.mode != M_IDLE);
     if (busy == 0u) {
       if (exhausted) break;
       continue;
     }
-    // ---- phase B: one traversal loop for every ray type -------------------------------------
-    while (__any_sync(kFullMask, L.node >= 0)) {
-      if (L.node >= 0) trav_step<COUNT>(c, L, stk);
+    // ---- phase B: one traversal loop for every ray type (hot state, FP32) -------------------
+    while (__any_sync(kFullMask, H.node >= 0)) {
+      if (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
     }
   }
   if (COUNT) {

@@ -36,7 +36,7 @@ void sim_free(void *p) { std::free(p); }
 
 int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, const rt_vec4 *lpos,
                const rt_vec4 *lcol, int nlights, const rt_render_params *params, const rt_frame_out *out,
-               unsigned long long *counters, int nthreads) {
+               unsigned long long *counters, int nthreads, unsigned *cost_nodes, unsigned *cost_tris) {
   using namespace rtb;
   std::string err;
   int st = check_blob(blob, bytes, err);
@@ -62,18 +62,25 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
     unsigned long long mine[C_COUNT] = {0};
     Ctx ct = c;
     ct.cnt = cnt;
-    int stk[kStackMax];
+    int stk[2 * kStackMax];
+    double cold_d[CD_NUM];
+    int cold_i[CI_NUM];
+    Cold<1> Cd;
+    Cd.db = cold_d;
+    Cd.ib = cold_i;
 #pragma omp for schedule(dynamic, 256)
     for (long long w = 0; w < slots; ++w) {
       int px, py;
       if (!work_to_pixel(ct, w, px, py)) continue;
-      Lane L;
-      L.mode = M_IDLE; L.node = -1;
-      begin_pixel<true>(ct, L, px, py);
-      while (L.mode != M_IDLE) {
-        if (L.node >= 0) trav_step<true>(ct, L, stk);
-        else advance<true>(ct, L);
+      Hot H;
+      H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1;
+      begin_pixel<true>(ct, H, Cd, px, py);
+      while (H.mode != M_IDLE) {
+        if (H.node >= 0) traverse<true>(ct, H, Cd, stk);
+        else advance<true>(ct, H, Cd);
       }
+      if (cost_nodes) cost_nodes[(size_t)py * ct.fp.cam.width + px] = cnt[C_NODES];
+      if (cost_tris) cost_tris[(size_t)py * ct.fp.cam.width + px] = cnt[C_TRI_FILTER];
       for (int k = 0; k < C_COUNT; ++k) { mine[k] += cnt[k]; cnt[k] = 0; }
     }
 #pragma omp critical

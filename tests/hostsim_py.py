@@ -15,7 +15,7 @@ def lib():
         _lib = C.CDLL(os.path.join(_HERE, "hostsim", "libhostsim.so"))
         _lib.sim_last_error.restype = C.c_char_p
         _lib.sim_render.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
-                                    C.c_void_p, C.c_void_p, C.c_int]
+                                    C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         for f in (_lib.sim_tri_filter, _lib.sim_box_test):
             f.argtypes = [_dp, _dp, _dp, _dp, _dp, C.c_double] if f is _lib.sim_tri_filter else [_dp, _dp, _dp, _dp, C.c_double]
         _lib.sim_tri_exact.argtypes = [_dp, _dp, _dp, _dp, _dp, _dp]
@@ -36,7 +36,7 @@ def flatten(host):
     return out
 
 
-def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, camera=None):
+def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, camera=None, cost=False):
     from my_raytracer_b200 import capi
     L = lib()
     blob = blob if blob is not None else flatten(host)
@@ -51,14 +51,18 @@ def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, 
                        t.ctypes.data if want_ids else None)
     p = host.params(spp_grid=spp_grid, flags=flags, tile=tile)
     cnt = (C.c_ulonglong * 10)()
+    cost_n = np.zeros((H, W), np.uint32); cost_t = np.zeros((H, W), np.uint32)
     lp, lc = host.lights_pos, host.lights_color
     st = L.sim_render(buf, len(blob), C.byref(cam), lp.ctypes.data, lc.ctypes.data, lp.shape[0], C.byref(p),
-                      C.byref(fo), cnt, 0)
+                      C.byref(fo), cnt, 0, cost_n.ctypes.data if cost else None, cost_t.ctypes.data if cost else None)
     if st != 0:
         raise RuntimeError("sim_render status %d: %s" % (st, L.sim_last_error().decode()))
     names = ("rays_primary", "rays_shadow", "rays_reflect", "box_tests", "tri_filter", "tri_exact", "object_tests",
              "shaded_hits", "texel_fetches", "nodes_visited")
-    return dict(rgba8=rgba, pixels=px, hit_id=ids, hit_t=t, counters=dict(zip(names, [int(c) for c in cnt])))
+    out = dict(rgba8=rgba, pixels=px, hit_id=ids, hit_t=t, counters=dict(zip(names, [int(c) for c in cnt])))
+    if cost:
+        out["cost_nodes"], out["cost_tris"] = cost_n, cost_t
+    return out
 
 
 def _v(x):

@@ -1,0 +1,29 @@
+"""Times kernel variants (my-raytracer_b200/variants/*.so) on Office 1080p and checks each against the
+first one bit for bit.  Usage: python tools/gpu_variants.py [names...]"""
+import os, subprocess, sys, json
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CHILD = r'''
+import os, sys, json, hashlib
+import numpy as np
+sys.path.insert(0, %r)
+import rtpkg
+rt = rtpkg.load()
+from my_raytracer_b200 import capi
+lib = rt.load_library()
+capi.check(lib.rt_init_device(0), lib)
+desc = rt.scenes.office()
+host = rt.HostScene(desc, lib)
+dev = rt.DeviceScene(host)
+ms = []
+for i in range(12):
+    out = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(), want=("rgba8", "hit_id", "hit_t"))
+    ms.append(dev.last_kernel_ms())
+h = hashlib.sha1(out["rgba8"].tobytes() + out["hit_id"].tobytes() + out["hit_t"].tobytes()).hexdigest()
+c = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(flags=capi.RT_FLAG_COUNTERS), want=("rgba8",))["counters"]
+print(json.dumps(dict(ms_min=min(ms[2:]), ms_med=sorted(ms[2:])[5], sha=h, nodes=c["nodes_visited"], filt=c["tri_filter"], exact=c["tri_exact"])))
+''' % ROOT
+names = sys.argv[1:] or sorted(f[:-3] for f in os.listdir(os.path.join(ROOT, "my-raytracer_b200", "variants")) if f.endswith(".so"))
+for n in names:
+    env = dict(os.environ, RT_B200_LIB=os.path.join(ROOT, "my-raytracer_b200", "variants", n + ".so"))
+    r = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True)
+    print(n, r.stdout.strip() or r.stderr[-600:], flush=True)
