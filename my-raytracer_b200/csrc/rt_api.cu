@@ -99,6 +99,9 @@ int adopt_blob(rt_scene *s) {
   s->view.texels = reinterpret_cast<const float *>(b + h.off_texels);
   s->view.num_nodes = h.num_nodes; s->view.num_tris = h.num_tris;
   s->view.num_meshes = h.num_meshes; s->view.num_objects = h.num_objects;
+  s->view.box_extent = h.box_extent;
+  s->view.maxx = reinterpret_cast<const NodeMaxX *>(b + h.off_maxx);
+  s->view.root_max_x = h.root_max_x;
   // texture objects over the blob's texel section ("textures go through texture objects")
   std::vector<MeshRec> meshes(h.num_meshes);
   if (h.num_meshes)
@@ -165,6 +168,12 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   const bool count = (fp.flags & RT_FLAG_COUNTERS) != 0;
   RT_CUDA(cudaMemsetAsync(s->d_work, 0, sizeof(unsigned long long), st));
   if (count) RT_CUDA(cudaMemsetAsync(s->d_counters, 0, sizeof(unsigned long long) * C_COUNT, st));
+#ifdef RT_TAILPROBE
+  {
+    unsigned long long init[C_COUNT] = {0, 0, ~0ull, 0, 0, 0, 0, 0, 0, 0};
+    RT_CUDA(cudaMemcpyAsync(s->d_counters, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  }
+#endif
   RT_CUDA(cudaEventRecord(s->ev0, st));
   if (count) render_kernel<true><<<s->grid_count, kBlockThreads, 0, st>>>(a);
   else render_kernel<false><<<s->grid_plain, kBlockThreads, 0, st>>>(a);
@@ -306,6 +315,9 @@ int rt_render_device(rt_scene *s, const rt_camera *camera, const rt_vec4 *d_ligh
   st = launch(s, fp, reinterpret_cast<const double *>(d_lights_pos), reinterpret_cast<const double *>(d_lights_color),
               fo, nullptr, 0, stx);
   if (st != RT_OK) return st;
+#ifdef RT_TAILPROBE
+  return fetch_counters(s, stx);
+#endif
   if (fp.flags & RT_FLAG_COUNTERS) return fetch_counters(s, stx);
   return RT_OK;
 }

@@ -61,12 +61,14 @@ template <int STRIDE> struct Cold {
 // ---- hot per-lane state (registers) -------------------------------------------------------------------
 struct Hot {
   RayF rf;
-  float thi;   // FP32 upper bound of the best distance, used for culling
+  float thi;   // FP32 upper bound of the best distance (triangle filter culling)
+  float thiS;  // thi with the slab test's relative margin (box culling), this_of()
   int best_id;
   int node;    // >= 0: interior NodeRec to visit next; < 0: traversal finished
   int sp;
   int mode;
   int found;   // any-hit result
+  int xpar;    // direction.x == 0 exactly: the reference's 0/0 slab quirk applies (rt_types.h NodeMaxX)
 };
 
 struct Mat {
@@ -140,8 +142,6 @@ RT_HD D3 fetch_texel(const SceneView &sv, int mesh, const MeshRec &mr, int px, i
 #endif
 }
 
-RT_HD float thi_of(double t) { return fminf(f_up(t) * (1.0f + 8.0f * kU32), FLT_MAX); }
-
 // ---------------------------------------------------------------------------------------
 // ray start: Ray(origin, dir) normalises dir (oracle/shim/utils/Ray.h), then the analytic
 // primitives are tested in list order (restated intersect_scene), then the BVH is entered.
@@ -152,7 +152,7 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   const D3 d = normalize(dir);
   C.set(CD_O, o);
   C.set(CD_D, d);
-  rayf_setup(H.rf, o, d);
+  rayf_setup(H.rf, o, d, c.sv.box_extent);
   H.mode = mode;
   H.best_id = -1;
   H.found = 0;
@@ -173,7 +173,11 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   }
   C.d(CD_BEST_T) = best;
   H.thi = thi_of(best);
+  H.thiS = this_of(H.thi);
   H.node = (sv.num_nodes > 0) ? 0 : -1;
+  H.xpar = (d.x == 0.0);
+  // root box, tested on entry by the reference (mybvh.cpp:157): (bb_max.x - o.x)/0 = NaN rejects it
+  if (H.xpar && o.x == sv.root_max_x) H.node = -1;
 }
 
 // FP64 confirmation of one filter survivor + nearest / any-hit bookkeeping.  Rare (~0.7 per ray).
@@ -196,12 +200,14 @@ template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const 
     C.d(CD_BEST_T) = h.t;
     H.best_id = i;
     H.thi = thi_of(h.t);
+    H.thiS = this_of(H.thi);
   }
 }
 
-template <bool COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int count) {
+// Triangles [first, last) of one leaf — or of two sibling leaves, whose ranges are adjacent (rt_types.h).
+template <bool COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last) {
   const bool exact_only = (c.fp.flags & 1) != 0;
-  for (int i = first; i < first + count; ++i) {
+  for (int i = first; i < last; ++i) {
     bump<COUNT>(c, C_TRI_FILTER);
     bool pass = exact_only;
     if (!exact_only) {
@@ -220,50 +226,59 @@ template <bool COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Co
   }
 }
 
+struct alignas(8) StackEntry {
+  int ref;   // NodeRec index of the postponed interior child
+  float tn;  // its entry distance (box_test's tn): stale entries are culled when popped
+};
+
 // One traversal step: one 64-byte node record (four 16-byte read-only loads), two conservative
-// slab tests, leaf children intersected at once, nearer interior child next, the other pushed
-// together with its entry distance so that stale entries are culled when popped.
+// slab tests (24 FMAs), hit leaf children intersected at once (ONE loop: sibling leaf ranges are
+// adjacent), nearer interior child next, the other pushed with its entry distance.
 // The kernel calls this from a WARP-UNIFORM loop (while (__any_sync(node >= 0)) if (node >= 0) step):
 // the vote re-converges the warp every iteration.  A per-lane `while (node >= 0)` loop lets lanes
 // drift out of phase and ran 2x slower on B200 (profiles/r01_variants.md).
-template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, int *stk) {
+template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   const char *np = reinterpret_cast<const char *>(c.sv.nodes) + (size_t)(unsigned)H.node * 64u;
   const F4 q0 = ld_f4(np), q1 = ld_f4(np + 16), q2 = ld_f4(np + 32);
   const I4 r = ld_i4(np + 48);
   bump<COUNT>(c, C_NODES);
   bump<COUNT>(c, C_BOX, 2);
-  // q0 = c0.min.xyz c0.max.x | q1 = c0.max.yz c1.min.xy | q2 = c1.min.z c1.max.xyz
-  const float b0mn[3] = {q0.x, q0.y, q0.z}, b0mx[3] = {q0.w, q1.x, q1.y};
-  const float b1mn[3] = {q1.z, q1.w, q2.x}, b1mx[3] = {q2.y, q2.z, q2.w};
+  // q0 = c0.ctr.xyz c0.half.x | q1 = c0.half.yz c1.ctr.xy | q2 = c1.ctr.z c1.half.xyz
+  const float b0c[3] = {q0.x, q0.y, q0.z}, b0h[3] = {q0.w, q1.x, q1.y};
+  const float b1c[3] = {q1.z, q1.w, q2.x}, b1h[3] = {q2.y, q2.z, q2.w};
   float tn0, tn1;
-  bool h0 = box_test(H.rf, b0mn, b0mx, H.thi, tn0);
-  bool h1 = box_test(H.rf, b1mn, b1mx, H.thi, tn1);
-  if (h0 && r.z > 0) {
-    leaf_test<COUNT>(c, H, C, r.x, r.z);
-    h0 = false;
+  bool h0 = box_test(H.rf, b0c, b0h, H.thiS, tn0);
+  bool h1 = box_test(H.rf, b1c, b1h, H.thiS, tn1);
+  if (H.xpar) { // rare (exactly axis-parallel rays): reproduce the reference's NaN rejection
+    const NodeMaxX mx = c.sv.maxx[H.node];
+    const double ox = C.d(CD_O);
+    h0 = h0 && !(ox == mx.c0_max_x);
+    h1 = h1 && !(ox == mx.c1_max_x);
   }
-  if (h1 && r.w > 0 && !H.found) {
-    leaf_test<COUNT>(c, H, C, r.y, r.w);
-    h1 = false;
+  const bool l0 = h0 && r.z > 0, l1 = h1 && r.w > 0;
+  if (l0 || l1) {
+    leaf_test<COUNT>(c, H, C, l0 ? r.x : r.y, l1 ? r.y + r.w : r.x + r.z);
+    if (H.found) { H.node = -1; return; }
+    h0 = h0 && !l0;
+    h1 = h1 && !l1;
+    // a nearer hit may have been found: the surviving interior sibling is re-checked when it is
+    // visited (its own children are culled against the new thiS)
   }
-  if (H.found) { H.node = -1; return; }
   int node, sp = H.sp;
   if (h0 && h1) {
     const bool far0 = tn1 < tn0;
-    stk[2 * sp] = far0 ? r.x : r.y;
-    stk[2 * sp + 1] = __float_as_int_rt(far0 ? tn0 : tn1);
+    stk[sp].ref = far0 ? r.x : r.y;
+    stk[sp].tn = fmaxf(tn0, tn1);
     ++sp;
     node = far0 ? r.y : r.x;
-  } else if (h0) {
-    node = r.x;
-  } else if (h1) {
-    node = r.y;
+  } else if (h0 || h1) {
+    node = h0 ? r.x : r.y;
   } else {
     node = -1;
     while (sp > 0) {
       --sp;
-      const float tn = __int_as_float_rt(stk[2 * sp + 1]);
-      if (tn <= H.thi) { node = stk[2 * sp]; break; } // else: culled, a nearer hit was found meanwhile
+      const StackEntry e = stk[sp];
+      if (e.tn <= H.thiS) { node = e.ref; break; } // else: culled, a nearer hit was found meanwhile
     }
   }
   H.node = node;
@@ -271,7 +286,7 @@ template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Co
 }
 
 // host/test build: run this lane's ray to completion
-template <bool COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, int *stk) {
+template <bool COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   while (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
 }
 

@@ -64,13 +64,24 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
 
   // ---- 1. walk the reference tree, number interior nodes in DFS pre-order -------------------
   std::vector<NodeRec> nodes;
+  std::vector<NodeMaxX> maxx;
   int max_depth = 0, max_leaf = 0, nodes_ref = 0, root_is_leaf = 0;
   std::vector<unsigned char> tri_seen(N > 0 ? N : 0, 0);
   const int cap = 2 * N - 1; // slots the reference allocates (mybvh.cpp:386)
-  auto box_of = [&](int r, float *mn, float *mx) {
+  double box_extent = 0.0;
+  // centre / half-extent form, outward: [ctr - half, ctr + half] (as real numbers) contains the FP64 box
+  auto box_of = [&](int r, float *ctr, float *half) {
     const rt_vec4 &a = bvh->bb_min_[r], &b = bvh->bb_max_[r];
-    mn[0] = round_down(a.x); mn[1] = round_down(a.y); mn[2] = round_down(a.z);
-    mx[0] = round_up(b.x);   mx[1] = round_up(b.y);   mx[2] = round_up(b.z);
+    const double lo[3] = {a.x, a.y, a.z}, hi[3] = {b.x, b.y, b.z};
+    for (int k = 0; k < 3; ++k) {
+      const float c = (float)(0.5 * (lo[k] + hi[k]));
+      const double need = std::fmax(hi[k] - (double)c, (double)c - lo[k]); // each difference: one FP64 rounding
+      float h = round_up(need > 0.0 ? need : 0.0);
+      h = std::nextafterf(h, std::numeric_limits<float>::infinity());        // covers that rounding
+      ctr[k] = c; half[k] = h;
+      const double e = std::fabs((double)c) + (double)h;
+      if (e > box_extent) box_extent = e;
+    }
   };
   auto leaf_ok = [&](int r) -> bool {
     const int f = bvh->firstTriIdx_[r], c = bvh->triCount_[r];
@@ -90,15 +101,17 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
       nodes_ref = 1;
       if (!leaf_ok(0)) { err = "flatten: root leaf range invalid"; return RT_ERR_BAD_SCENE; }
       NodeRec n;
-      box_of(0, n.c0_min, n.c0_max);
-      for (int k = 0; k < 3; ++k) n.c1_min[k] = 1e30f, n.c1_max[k] = -1e30f;
+      box_of(0, n.c0_ctr, n.c0_half);
+      for (int k = 0; k < 3; ++k) n.c1_ctr[k] = 0.0f, n.c1_half[k] = -1e30f;
       n.ref0 = bvh->firstTriIdx_[0]; n.cnt0 = bvh->triCount_[0];
       n.ref1 = 0; n.cnt1 = 0;
       nodes.push_back(n);
+      maxx.push_back(NodeMaxX{bvh->bb_max_[0].x, -1e300});
       max_depth = 1;
     } else {
       std::vector<Walk> todo;
       nodes.emplace_back();
+      maxx.emplace_back();
       todo.push_back({0, 0, 1});
       nodes_ref = 1;
       while (!todo.empty()) {
@@ -113,8 +126,8 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
         nodes_ref += 2;
         if (nodes_ref > cap) { err = "flatten: BVH has a cycle or more than 2N-1 nodes"; return RT_ERR_BAD_SCENE; }
         NodeRec n;
-        box_of(l, n.c0_min, n.c0_max);
-        box_of(l + 1, n.c1_min, n.c1_max);
+        box_of(l, n.c0_ctr, n.c0_half);
+        box_of(l + 1, n.c1_ctr, n.c1_half);
         int ref[2], cnt[2];
         // right child first onto the stack so that the LEFT subtree gets the next indices
         // (DFS pre-order: a left descent walks contiguous records)
@@ -131,13 +144,21 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
           } else {
             child_flat[s] = (int)nodes.size();
             nodes.emplace_back();
+            maxx.emplace_back();
             ref[s] = child_flat[s]; cnt[s] = 0;
           }
         }
         if (child_flat[1] >= 0) todo.push_back({l + 1, child_flat[1], w.depth + 1});
         if (child_flat[0] >= 0) todo.push_back({l, child_flat[0], w.depth + 1});
+        if (cnt[0] > 0 && cnt[1] > 0 && ref[1] != ref[0] + cnt[0]) {
+          // BVH::inplace_partitionSoA (mybvh.cpp:481-513) always yields adjacent sibling ranges; the
+          // kernel tests two sibling leaves as ONE range
+          err = "flatten: sibling leaves with non-adjacent triangle ranges at node " + std::to_string(w.ref_node);
+          return RT_ERR_BAD_SCENE;
+        }
         n.ref0 = ref[0]; n.cnt0 = cnt[0]; n.ref1 = ref[1]; n.cnt1 = cnt[1];
         nodes[w.flat_idx] = n;
+        maxx[w.flat_idx] = NodeMaxX{bvh->bb_max_[l].x, bvh->bb_max_[l + 1].x};
       }
     }
     for (int i = 0; i < N; ++i)
@@ -280,6 +301,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.root_is_leaf = root_is_leaf; h.max_depth = max_depth; h.max_leaf = max_leaf; h.num_nodes_ref = nodes_ref;
   h.num_texels = num_texels;
   h.scene_extent = (float)extent;
+  h.box_extent = round_up(box_extent);
   size_t off = align_up(sizeof(BlobHeader), kSectionAlign);
   h.off_nodes = off;   off = align_up(off + nodes.size() * sizeof(NodeRec), kSectionAlign);
   h.off_filter = off;  off = align_up(off + filt.size() * sizeof(TriFilter), kSectionAlign);
@@ -288,10 +310,13 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.off_meshes = off;  off = align_up(off + meshes.size() * sizeof(MeshRec), kSectionAlign);
   h.off_objects = off; off = align_up(off + objs.size() * sizeof(ObjectRec), kSectionAlign);
   h.off_texels = off;  off = align_up(off + num_texels * 4 * sizeof(float), kSectionAlign);
+  h.off_maxx = off;    off = align_up(off + maxx.size() * sizeof(NodeMaxX), kSectionAlign);
+  h.root_max_x = N > 0 ? bvh->bb_max_[0].x : 0.0;
   h.total_bytes = off;
   blob.assign(off, 0);
   std::memcpy(blob.data(), &h, sizeof(h));
   if (!nodes.empty()) std::memcpy(blob.data() + h.off_nodes, nodes.data(), nodes.size() * sizeof(NodeRec));
+  if (!maxx.empty()) std::memcpy(blob.data() + h.off_maxx, maxx.data(), maxx.size() * sizeof(NodeMaxX));
   if (N > 0) {
     std::memcpy(blob.data() + h.off_filter, filt.data(), filt.size() * sizeof(TriFilter));
     std::memcpy(blob.data() + h.off_exact, exact.data(), exact.size() * sizeof(TriExact));
@@ -319,7 +344,8 @@ int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
                   h.off_shade + (size_t)h.num_tris * sizeof(TriShade) <= h.off_meshes &&
                   h.off_meshes + (size_t)h.num_meshes * sizeof(MeshRec) <= h.off_objects &&
                   h.off_objects + (size_t)h.num_objects * sizeof(ObjectRec) <= h.off_texels &&
-                  h.off_texels + h.num_texels * 16 <= h.total_bytes;
+                  h.off_texels + h.num_texels * 16 <= h.off_maxx &&
+                  h.off_maxx + (size_t)h.num_nodes * sizeof(NodeMaxX) <= h.total_bytes;
   if (!ok) { err = "blob: section table inconsistent"; return RT_ERR_BAD_SCENE; }
   return RT_OK;
 }
@@ -336,7 +362,10 @@ SceneView view_of_blob(const unsigned char *blob) {
   v.objects = reinterpret_cast<const ObjectRec *>(blob + h.off_objects);
   v.texels = reinterpret_cast<const float *>(blob + h.off_texels);
   v.tex_objs = nullptr;
+  v.maxx = reinterpret_cast<const NodeMaxX *>(blob + h.off_maxx);
+  v.root_max_x = h.root_max_x;
   v.num_nodes = h.num_nodes; v.num_tris = h.num_tris; v.num_meshes = h.num_meshes; v.num_objects = h.num_objects;
+  v.box_extent = h.box_extent; v.pad = 0;
   return v;
 }
 

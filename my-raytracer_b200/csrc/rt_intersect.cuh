@@ -1,8 +1,8 @@
 // rt_intersect.cuh — intersection primitives of the hot path.
 //
-//   box2_test        conservative FP32 slab test of the two child boxes of a NodeRec
-//                    (replaces BVH::intersectAABB mybvh.cpp:99-135 / intersectAABB_device
-//                    mytracer_gpu.cu:548-596: no divides, near/far planes picked by ray sign,
+//   box_test         conservative FP32 slab test of one child box of a NodeRec, centre/half-extent
+//                    form (replaces BVH::intersectAABB mybvh.cpp:99-135 / intersectAABB_device
+//                    mytracer_gpu.cu:548-596: 9 FMAs, no divides, no selection by ray sign,
 //                    culls against the current best distance)
 //   tri_filter       conservative FP32 Moeller-Trumbore filter with a running error bound
 //   tri_exact        FP64 confirmation == Mesh::intersect_triangle (mymesh.cpp:176-236)
@@ -17,11 +17,12 @@ namespace rtb {
 
 // Per-ray FP32 traversal constants.
 struct RayF {
-  float ox, oy, oz;    // origin rounded to FP32
-  float dx, dy, dz;    // direction rounded to FP32
+  float ox, oy, oz;    // origin rounded to FP32            (triangle filter)
+  float dx, dy, dz;    // direction rounded to FP32         (triangle filter)
   float ix, iy, iz;    // 1/d with |d| clamped to >= 1e-20 (no inf/NaN ever enters the slab test)
-  float lox, loy, loz; // -o*i - 4u|o*i|   (added to near-plane products)
-  float hix, hiy, hiz; // -o*i + 4u|o*i|   (added to far-plane products)
+  float ax, ay, az;    // |1/d|
+  float nx, ny, nz;    // -o*i - s   (near planes),  s = per-axis absolute slack, see rayf_setup
+  float fx, fy, fz;    // -o*i + s   (far planes)
   float o1n;           // |ox|+|oy|+|oz|  (triangle filter error bound)
 };
 
@@ -31,35 +32,52 @@ RT_HD float safe_rcp(float d) {
   return copysignf(1.0f / c, d);
 }
 
-RT_HD void rayf_setup(RayF &r, const D3 &o, const D3 &d) {
+// E = SceneView::box_extent: upper bound on |ctr| + half of every child box (every axis).
+RT_HD void rayf_setup(RayF &r, const D3 &o, const D3 &d, float E) {
   r.ox = (float)o.x; r.oy = (float)o.y; r.oz = (float)o.z;
   r.dx = (float)d.x; r.dy = (float)d.y; r.dz = (float)d.z;
   r.ix = safe_rcp(r.dx); r.iy = safe_rcp(r.dy); r.iz = safe_rcp(r.dz);
+  r.ax = fabsf(r.ix); r.ay = fabsf(r.iy); r.az = fabsf(r.iz);
   const float px = -r.ox * r.ix, py = -r.oy * r.iy, pz = -r.oz * r.iz;
-  const float k = 4.0f * kU32;
-  // slack covers the rounding of o (u|o|) and of the product o*i (u|o*i|), see DESIGN.md
-  const float sx = k * fabsf(px) , sy = k * fabsf(py), sz = k * fabsf(pz);
-  r.lox = px - sx - FLT_MIN; r.loy = py - sy - FLT_MIN; r.loz = pz - sz - FLT_MIN;
-  r.hix = px + sx + FLT_MIN; r.hiy = py + sy + FLT_MIN; r.hiz = pz + sz + FLT_MIN;
+  // Absolute error of a computed slab distance  fl(c*i + fl(p -+ s -+ h|i|))  against the exact
+  // ((c -+ h) - o)/d, beyond a few-ulp RELATIVE error (covered by kFarSlack and thi's margin):
+  //   rounding of o to FP32 and of p = -o*i:  2u|o||i| ;  rounding of the inner FMA:
+  //   u|p -+ h|i|| <= u(|o| + E)|i| ;  the outer FMA rounds relative to its result.
+  // Per-axis bound s = 6u(|o| + E)|i| (+ FLT_MIN), a spatial slack of 6u(|o| + E): it stays on its own
+  // axis, so a ray parallel to one slab (|i| = 1e20) keeps full culling on the other two.
+  const float k = 6.0f * kU32; // 4u from the analysis above + margin
+  const float sx = k * (fabsf(r.ox) + E) * r.ax + FLT_MIN;
+  const float sy = k * (fabsf(r.oy) + E) * r.ay + FLT_MIN;
+  const float sz = k * (fabsf(r.oz) + E) * r.az + FLT_MIN;
+  r.nx = px - sx; r.ny = py - sy; r.nz = pz - sz;
+  r.fx = px + sx; r.fy = py + sy; r.fz = pz + sz;
   r.o1n = fabsf(r.ox) + fabsf(r.oy) + fabsf(r.oz);
 }
 
-// relative slack on the far distance: covers the 4u|t| rounding of every slab distance
+// relative slack on the far distance: covers the few-ulp relative rounding of every slab distance
 constexpr float kFarSlack = 1.0f + 64.0f * kU32;
 
-// Entry distance (conservative lower bound) of one child box; hit iff max(tn,0) <= min(tf', thi)
-RT_HD bool box_test(const RayF &r, const float *bmin, const float *bmax, float thi, float &tn) {
-  const float nx = r.ix >= 0.f ? bmin[0] : bmax[0], fx = r.ix >= 0.f ? bmax[0] : bmin[0];
-  const float ny = r.iy >= 0.f ? bmin[1] : bmax[1], fy = r.iy >= 0.f ? bmax[1] : bmin[1];
-  const float nz = r.iz >= 0.f ? bmin[2] : bmax[2], fz = r.iz >= 0.f ? bmax[2] : bmin[2];
-  const float tnx = fmaf(nx, r.ix, r.lox), tfx = fmaf(fx, r.ix, r.hix);
-  const float tny = fmaf(ny, r.iy, r.loy), tfy = fmaf(fy, r.iy, r.hiy);
-  const float tnz = fmaf(nz, r.iz, r.loz), tfz = fmaf(fz, r.iz, r.hiz);
+// Upper bounds used for culling: thi >= best t (triangle filter), thiS = thi*(1+16u) (box test).
+RT_HD float thi_of(double t) { return fminf(f_up(t) * (1.0f + 8.0f * kU32), FLT_MAX); }
+RT_HD float this_of(float thi) { return fminf(thi * (1.0f + 16.0f * kU32), FLT_MAX); }
+
+// Conservative slab test of one child box in centre/half-extent form (replaces BVH::intersectAABB
+// mybvh.cpp:99-135 / intersectAABB_device mytracer_gpu.cu:548-596).  Twelve FMAs, no divides and
+// no selection by ray sign:
+//     t_near = c*i + (n - h|i|),   t_far = c*i + (f + h|i|)        per axis
+// hit iff max(tn, 0) <= min(tf*kFarSlack + FLT_MIN, thiS) with tn = max3(t_near), tf = min3(t_far).
+// tf < 0 (box behind the ray): tf*slack stays negative < max(tn, 0): rejected.
+// tn (unclamped) orders the two children and is what the stack keeps.
+RT_HD bool box_test(const RayF &r, const float *c, const float *h, float thiS, float &tn) {
+  const float tnx = fmaf(c[0], r.ix, fmaf(h[0], -r.ax, r.nx));
+  const float tny = fmaf(c[1], r.iy, fmaf(h[1], -r.ay, r.ny));
+  const float tnz = fmaf(c[2], r.iz, fmaf(h[2], -r.az, r.nz));
+  const float tfx = fmaf(c[0], r.ix, fmaf(h[0], r.ax, r.fx));
+  const float tfy = fmaf(c[1], r.iy, fmaf(h[1], r.ay, r.fy));
+  const float tfz = fmaf(c[2], r.iz, fmaf(h[2], r.az, r.fz));
   tn = fmax3(tnx, tny, tnz);
   const float tf = fmin3(tfx, tfy, tfz);
-  // tf < 0 (box behind the ray): tf*slack stays negative < max(tn,0): rejected
-  const float tf2 = fminf(tf * kFarSlack + FLT_MIN, thi);
-  return fmaxf(tn, 0.0f) <= tf2;
+  return fmaxf(tn, 0.0f) <= fminf(fmaf(tf, kFarSlack, FLT_MIN), thiS);
 }
 
 // FP32 conservative triangle filter.  thi = upper bound (FP32, rounded up) on the ray

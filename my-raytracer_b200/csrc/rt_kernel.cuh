@@ -48,6 +48,10 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
 #pragma unroll
     for (int k = 0; k < C_COUNT; ++k) cnt[k] = 0;
   }
+#ifdef RT_TAILPROBE
+  unsigned long long t_probe0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_probe0));
+#endif
   Ctx c;
   c.sv = a.sv; c.fp = a.fp;
   c.light_pos = a.light_pos; c.light_col = a.light_col;
@@ -75,13 +79,14 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
   C.db = a.scratch_d + (size_t)blockIdx.x * kBlockThreads + threadIdx.x;
   C.ib = a.scratch_i + (size_t)blockIdx.x * kBlockThreads + threadIdx.x;
 #endif
-  int stk[2 * kStackMax];
+  StackEntry stk[kStackMax];
   Hot H;
   H.mode = M_IDLE;
   H.node = -1;
   H.sp = 0;
   H.found = 0;
   H.best_id = -1;
+  H.xpar = 0;
   const long long slots = work_slots(c);
   const unsigned lane = threadIdx.x & 31u;
   bool exhausted = false; // warp-uniform
@@ -121,6 +126,19 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     for (int k = 0; k < C_COUNT; ++k)
       if (cnt[k]) atomicAdd(a.counters + k, (unsigned long long)cnt[k]);
   }
+#ifdef RT_TAILPROBE
+  // experiment (tools/gpu_tailprobe.py): when does each warp run out of work?  counters[0] = sum of
+  // warp end times, [1] = max, [2] = min start, [3] = number of warps (globaltimer ns)
+  if (!COUNT && lane == 0) {
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    atomicAdd(a.counters + 0, t1 - t_probe0);
+    atomicMax(a.counters + 1, t1);
+    atomicMin(a.counters + 2, t_probe0);
+    atomicAdd(a.counters + 3, 1ull);
+    atomicAdd(a.counters + 4, t_probe0);
+  }
+#endif
 }
 
 // Contrast test of the adaptive supersampling pass (adaptive_supersampling_device,

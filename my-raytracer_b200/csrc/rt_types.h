@@ -3,12 +3,14 @@
 //
 // One contiguous, 512-byte-sectioned blob (so it can be broadcast with a single NCCL call):
 //
-//   BlobHeader | NodeRec[] | TriFilter[] | TriExact[] | TriShade[] | MeshRec[] | ObjectRec[] | texels
+//   BlobHeader | NodeRec[] | TriFilter[] | TriExact[] | TriShade[] | MeshRec[] | ObjectRec[] | texels | NodeMaxX[]
 //
 // * NodeRec   64 B  (4 x float4): one record per INTERIOR node of the reference's median-split
-//             tree (mybvh.h:49-55 / mybvh.cpp:438-472) holding BOTH child boxes, outward-
-//             rounded to FP32, plus the two child references.  Same topology, half the
-//             dependent loads of the reference's 76 B/node five-array layout.
+//             tree (mybvh.h:49-55 / mybvh.cpp:438-472) holding BOTH child boxes in FP32
+//             centre / half-extent form (outward-rounded: [c-h, c+h] contains the FP64 box),
+//             plus the two child references.  Same topology, half the dependent loads of the
+//             reference's 76 B/node five-array layout; the centre/half form turns the slab test
+//             into 9 FMAs per box with no min/max selection by ray sign (rt_intersect.cuh).
 // * TriFilter 48 B  (3 x float4): FP32 Moeller-Trumbore operands + per-triangle error-bound
 //             constants, BVH order.  A conservative filter: it never rejects a triangle the
 //             reference's FP64 test (mymesh.cpp:176-236) accepts.
@@ -17,6 +19,11 @@
 // * TriShade 128 B: normals (face or 3 vertex normals), UVs, mesh id — read once per shaded hit.
 // * MeshRec  128 B: material + draw mode + texture descriptor (mydata.h:57-71).
 // * ObjectRec: analytic primitives (Raytracer::objects_), FP64.
+// * NodeMaxX  16 B: the FP64 bb_max_.x of both children, read ONLY by rays whose direction.x is exactly
+//             0: the reference's slab test (mybvh.cpp:99-135) computes (bb_max.x - o.x)/0 = 0/0 = NaN when
+//             o.x == bb_max.x, the NaN survives std::min and the box is REJECTED (with its subtree).
+//             The kernel reproduces that one quirk so that primitive ids stay bit-exact on such rays
+//             (e.g. the centre pixel column of a symmetric view over a grid line).
 #ifndef RTB_TYPES_H
 #define RTB_TYPES_H
 #include <stddef.h>
@@ -25,17 +32,20 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 3;
+constexpr uint32_t kBlobVersion = 4;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
 
 struct alignas(16) NodeRec {
   // c0 = left child (leftChildIdx_), c1 = right child (leftChildIdx_ + 1)
-  float c0_min[3], c0_max[3];
-  float c1_min[3], c1_max[3];
+  // ctr = box centre, half = half extent >= 0 (an empty child has half = -1e30: never hit)
+  float c0_ctr[3], c0_half[3];
+  float c1_ctr[3], c1_half[3];
   // ref >= 0.  cnt == 0: ref is the NodeRec index of an interior child.
   //            cnt  > 0: leaf child with triangles [ref, ref + cnt) in BVH order.
+  // Two sibling leaves always own adjacent ranges (ref1 == ref0 + cnt0: the in-place partition of
+  // mybvh.cpp:481-513 splits one range in two); the flattener rejects anything else.
   int32_t ref0, ref1, cnt0, cnt1;
 };
 static_assert(sizeof(NodeRec) == 64, "NodeRec must be 64 bytes");
@@ -81,6 +91,11 @@ struct alignas(16) ObjectRec {
 };
 static_assert(sizeof(ObjectRec) == 160, "ObjectRec must be 160 bytes");
 
+struct alignas(16) NodeMaxX {
+  double c0_max_x, c1_max_x;
+};
+static_assert(sizeof(NodeMaxX) == 16, "NodeMaxX must be 16 bytes");
+
 struct BlobHeader {
   uint32_t magic, version;
   uint64_t total_bytes;
@@ -89,8 +104,11 @@ struct BlobHeader {
   uint64_t num_texels;
   uint64_t off_nodes, off_filter, off_exact, off_shade, off_meshes, off_objects, off_texels;
   float scene_extent; // max |coordinate| over all vertices (diagnostics)
-  float pad_f[3];
-  uint64_t reserved[6];
+  float box_extent;   // >= |ctr| + half of every child box, every axis (slab-test error bound)
+  float pad_f[2];
+  uint64_t off_maxx;   // NodeMaxX[num_nodes]
+  double root_max_x;   // bb_max_.x of reference node 0 (tested on entry, mybvh.cpp:157)
+  uint64_t reserved[4];
 };
 static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
 
@@ -104,7 +122,11 @@ struct SceneView {
   const ObjectRec *objects;
   const float *texels; // 4 floats per texel (host/test build); the kernel uses tex_objs instead
   const unsigned long long *tex_objs; // cudaTextureObject_t per mesh (0 when untextured)
+  const NodeMaxX *maxx;
+  double root_max_x;
   int32_t num_nodes, num_tris, num_meshes, num_objects;
+  float box_extent;
+  int32_t pad;
 };
 
 struct CameraRec {

@@ -62,7 +62,7 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
     unsigned long long mine[C_COUNT] = {0};
     Ctx ct = c;
     ct.cnt = cnt;
-    int stk[2 * kStackMax];
+    StackEntry stk[kStackMax];
     double cold_d[CD_NUM];
     int cold_i[CI_NUM];
     Cold<1> Cd;
@@ -73,7 +73,7 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
       int px, py;
       if (!work_to_pixel(ct, w, px, py)) continue;
       Hot H;
-      H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1;
+      H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.xpar = 0;
       begin_pixel<true>(ct, H, Cd, px, py);
       while (H.mode != M_IDLE) {
         if (H.node >= 0) traverse<true>(ct, H, Cd, stk);
@@ -107,9 +107,8 @@ int sim_tri_filter(const double *p0, const double *p1, const double *p2, const d
   f.k_t = up(std::fmax(8.0 * u * a * b, tiny));
   f.k_det = up(std::fmax(64.0 * u * a * b, tiny));
   RayF r;
-  rayf_setup(r, ld3(o), ld3(d));
-  const float t = fminf(f_up(thi) * (1.0f + 8.0f * kU32), FLT_MAX);
-  return tri_filter(r, f, t) ? 1 : 0;
+  rayf_setup(r, ld3(o), ld3(d), 0.0f);
+  return tri_filter(r, f, thi_of(thi)) ? 1 : 0;
 }
 
 int sim_tri_exact(const double *p0, const double *p1, const double *p2, const double *o, const double *d,
@@ -121,19 +120,28 @@ int sim_tri_exact(const double *p0, const double *p1, const double *p2, const do
   return hit ? 1 : 0;
 }
 
-// conservative FP32 box test against an FP64 box (rounded outward like the flattener)
-int sim_box_test(const double *bmin, const double *bmax, const double *o, const double *d, double thi) {
+// conservative FP32 box test against an FP64 box, encoded in centre/half-extent form by the flattener
+// (a one-triangle-pair scene would do the same; this calls the flattener's arithmetic through a tiny BVH)
+int sim_box_test(const double *bmin, const double *bmax, const double *o, const double *d, double thi,
+                 double extent_scale) {
   using namespace rtb;
-  float mn[3], mx[3];
+  float ctr[3], half[3];
+  double E = 0.0;
   for (int k = 0; k < 3; ++k) {
-    mn[k] = (float)bmin[k]; if ((double)mn[k] > bmin[k]) mn[k] = nextafterf(mn[k], -INFINITY);
-    mx[k] = (float)bmax[k]; if ((double)mx[k] < bmax[k]) mx[k] = nextafterf(mx[k], INFINITY);
+    const float cc = (float)(0.5 * (bmin[k] + bmax[k]));
+    const double need = std::fmax(bmax[k] - (double)cc, (double)cc - bmin[k]);
+    float h = (float)need; if ((double)h < need) h = nextafterf(h, INFINITY);
+    h = nextafterf(h, INFINITY);
+    ctr[k] = cc; half[k] = h;
+    E = std::fmax(E, std::fabs((double)cc) + (double)h);
   }
+  E *= extent_scale; // the scene's box_extent is >= this box's
+  float Ef = (float)E; if ((double)Ef < E) Ef = nextafterf(Ef, INFINITY);
   RayF r;
-  rayf_setup(r, ld3(o), ld3(d));
+  rayf_setup(r, ld3(o), ld3(d), Ef);
   float tn;
-  const float t = fminf(f_up(thi) * (1.0f + 8.0f * kU32), FLT_MAX);
-  return box_test(r, mn, mx, t, tn) ? 1 : 0;
+  const float t = thi_of(thi);
+  return box_test(r, ctr, half, this_of(t), tn) ? 1 : 0;
 }
 
 } // extern "C"

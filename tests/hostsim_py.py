@@ -17,7 +17,7 @@ def lib():
         _lib.sim_render.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         for f in (_lib.sim_tri_filter, _lib.sim_box_test):
-            f.argtypes = [_dp, _dp, _dp, _dp, _dp, C.c_double] if f is _lib.sim_tri_filter else [_dp, _dp, _dp, _dp, C.c_double]
+            f.argtypes = [_dp, _dp, _dp, _dp, _dp, C.c_double] if f is _lib.sim_tri_filter else [_dp, _dp, _dp, _dp, C.c_double, C.c_double]
         _lib.sim_tri_exact.argtypes = [_dp, _dp, _dp, _dp, _dp, _dp]
         _lib.sim_free.argtypes = [C.c_void_p]
     return _lib
@@ -79,5 +79,6 @@ def tri_exact(p0, p1, p2, o, d):
     return bool(hit), out
 
 
-def box_test(bmin, bmax, o, d, thi):
-    return bool(lib().sim_box_test(_v(bmin), _v(bmax), _v(o), _v(d), float(thi)))
+def box_test(bmin, bmax, o, d, thi, extent_scale=1.0):
+    """extent_scale > 1 emulates a box that is small against the scene's box_extent (larger slack)."""
+    return bool(lib().sim_box_test(_v(bmin), _v(bmax), _v(o), _v(d), float(thi), float(extent_scale)))

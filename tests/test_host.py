@@ -126,9 +126,23 @@ def test_flatten_structure(rt, lib, sim):
     # root record = the two children of reference node 0, conservatively rounded
     l = host.bvh_arrays["left"][0]
     mn, mx = host.bvh_arrays["bbmin"], host.bvh_arrays["bbmax"]
-    assert (nodes[0, 0:3] <= mn[l, :3]).all() and (nodes[0, 3:6] >= mx[l, :3]).all()
-    assert (nodes[0, 6:9] <= mn[l + 1, :3]).all() and (nodes[0, 9:12] >= mx[l + 1, :3]).all()
-    assert np.abs(nodes[0, 0:3] - mn[l, :3]).max() < 1e-5
+    # (centre / half-extent form: [c - h, c + h] evaluated in FP64 must contain the FP64 box, tightly)
+    n0 = nodes[0].astype(np.float64)
+    for k, ref in ((0, l), (6, l + 1)):
+        c, hh = n0[k:k + 3], n0[k + 3:k + 6]
+        assert (c - hh <= mn[ref, :3]).all() and (c + hh >= mx[ref, :3]).all()
+        assert np.abs((c - hh) - mn[ref, :3]).max() < 1e-5 and np.abs((c + hh) - mx[ref, :3]).max() < 1e-5
+    # every record of the tree: same containment against the reference boxes (walk both trees together)
+    todo = [(0, 0)]
+    while todo:
+        ref, flat = todo.pop()
+        lc = host.bvh_arrays["left"][ref]
+        rec = nodes[flat].astype(np.float64)
+        for s_, k in ((0, 0), (1, 6)):
+            c, hh = rec[k:k + 3], rec[k + 3:k + 6]
+            assert (c - hh <= mn[lc + s_, :3]).all() and (c + hh >= mx[lc + s_, :3]).all()
+            if refs[flat][2 + s_] == 0:
+                todo.append((lc + s_, int(refs[flat][s_])))
 
 
 def test_flatten_rejects_bad_input(rt, lib, sim):

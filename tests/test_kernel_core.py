@@ -113,7 +113,43 @@ def test_box_test_is_conservative(sim, orc, oracle_kind):
         if hit:
             n_acc += 1
             assert sim.box_test(mn, mx, o, d, 1e300), (i, mn, mx, o, d)
+            assert sim.box_test(mn, mx, o, d, 1e300, extent_scale=50.0), (i, mn, mx, o, d)
     assert n_acc > 1500
+
+
+def test_box_test_culls_and_keeps_with_finite_tmax(sim):
+    """Property with a finite best distance: a box that contains a point of the ray at parameter t0 must
+    be accepted for every thi >= t0 (incl. grazing, near-parallel rays and origins on a box face), and a
+    box that is clearly farther than thi must be culled (the test is a useful filter)."""
+    rng = np.random.default_rng(11)
+    kept = culled = far = 0
+    for i in range(8000):
+        s = 10.0 ** rng.uniform(-2, 2)
+        mn = rng.uniform(-1, 1, 3) * s
+        mx = mn + rng.uniform(0, 1, 3) * s * (10.0 ** rng.uniform(-3, 0))
+        q = mn + (mx - mn) * rng.uniform(0, 1, 3)          # a point inside the box
+        if i % 3 == 0:
+            k = rng.integers(0, 3); q[k] = mn[k] if i % 2 else mx[k]   # on a face
+        d = rng.normal(size=3)
+        if i % 4 == 0:
+            d[rng.integers(0, 3)] *= 10.0 ** rng.uniform(-14, -4)     # near-parallel to a slab
+        if i % 7 == 0:
+            d[rng.integers(0, 3)] = 0.0
+        if not d.any():
+            continue
+        d /= np.linalg.norm(d)
+        t0 = 10.0 ** rng.uniform(-3, 2) * s
+        o = q - t0 * d
+        # the exact point q = o + t0 d lies in the box up to FP64 rounding of o: accept at thi = t0 (1 + 1e-12)
+        assert sim.box_test(mn, mx, o, d, t0 * (1 + 1e-12)), (i, mn, mx, o, d, t0)
+        assert sim.box_test(mn, mx, o, d, t0 * (1 + 1e-12), extent_scale=20.0)
+        kept += 1
+        # entry distance is at least t0 - diag; a best distance well before that must cull the box
+        diag = np.linalg.norm(mx - mn)
+        if t0 > 4 * diag + 1e-3 * s:
+            far += 1
+            culled += not sim.box_test(mn, mx, o, d, 0.5 * (t0 - diag))
+    assert kept > 7000 and far > 1000 and culled > 0.9 * far
 
 
 def test_tie_break_is_visit_order_independent(rt, lib, sim, orc, oracle_kind):
@@ -133,3 +169,18 @@ def test_tie_break_is_visit_order_independent(rt, lib, sim, orc, oracle_kind):
         r = sim.render(host)
         ref = orc.OracleScene(desc, oracle_kind).render()
         assert np.array_equal(r["hit_id"], ref["ids"]) and (ref["ids"] >= 0).sum() > 40
+
+
+def test_axis_parallel_rays_reproduce_reference_nan_quirk(rt, lib, sim, orc, oracle_kind):
+    """Centre pixel column of a symmetric view over a grid line: direction.x == 0 exactly and origin.x equals
+    box faces, where the reference's slab test evaluates 0/0 = NaN and rejects the box whose bb_max.x equals
+    origin.x (mybvh.cpp:99-135).  The ids must still be bit-exact (rt_types.h NodeMaxX)."""
+    desc = rt.scenes.REGISTRY["scatter"](width=64, height=36, n_objects=40)
+    host = rt.HostScene(desc, lib)
+    r = sim.render(host)
+    ref = orc.OracleScene(desc, oracle_kind).render()
+    d = np.asarray(desc.camera["eye"], float)
+    assert np.array_equal(r["hit_id"], ref["ids"]) and np.array_equal(r["hit_t"], ref["t"])
+    # the quirk is actually exercised: without it the lower-index twin triangle would win on that column
+    blob_ids = r["hit_id"][:, 32]
+    assert (blob_ids >= 0).any()
