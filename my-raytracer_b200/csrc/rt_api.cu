@@ -11,6 +11,7 @@
 #include "rt_kernel.cuh"
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -57,6 +58,7 @@ struct rt_scene {
   int *d_list = nullptr; // supersampling pixel list
   size_t cap_list = 0;
   int grid_plain = 0, grid_count = 0;
+  size_t extra_smem = 0;
   rt_counters counters;
   rt_scene_info info;
   bool timed = false;
@@ -136,8 +138,16 @@ int adopt_blob(rt_scene *s) {
   cudaDeviceProp prop;
   RT_CUDA(cudaGetDeviceProperties(&prop, s->device));
   int occ0 = 0, occ1 = 0;
-  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, render_kernel<false>, kBlockThreads, 0));
-  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, render_kernel<true>, kBlockThreads, 0));
+  // experiments only (tools/gpu_occupancy.py): RT_EXTRA_SMEM=<bytes> of unused dynamic shared memory
+  // throttles the resident CTAs per SM
+  s->extra_smem = 0;
+  if (const char *e = std::getenv("RT_EXTRA_SMEM")) s->extra_smem = (size_t)std::atol(e);
+  if (s->extra_smem) {
+    RT_CUDA(cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+    RT_CUDA(cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+  }
+  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, render_kernel<false>, kBlockThreads, s->extra_smem));
+  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, render_kernel<true>, kBlockThreads, s->extra_smem));
   s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
   s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
   {
@@ -175,8 +185,8 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   }
 #endif
   RT_CUDA(cudaEventRecord(s->ev0, st));
-  if (count) render_kernel<true><<<s->grid_count, kBlockThreads, 0, st>>>(a);
-  else render_kernel<false><<<s->grid_plain, kBlockThreads, 0, st>>>(a);
+  if (count) render_kernel<true><<<s->grid_count, kBlockThreads, s->extra_smem, st>>>(a);
+  else render_kernel<false><<<s->grid_plain, kBlockThreads, s->extra_smem, st>>>(a);
   RT_CUDA(cudaGetLastError());
   RT_CUDA(cudaEventRecord(s->ev1, st));
   s->timed = true;
