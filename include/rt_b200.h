@@ -146,6 +146,8 @@ typedef struct rt_counters {
   unsigned long long shaded_hits;    /* lighting() evaluations */
   unsigned long long texel_fetches;
   unsigned long long nodes_visited;  /* interior node records loaded */
+  unsigned long long shadow_trivial; /* shadow rays (counted in rays_shadow) resolved without traversal:
+                                        the light's contribution is exactly zero whatever the occlusion */
 } rt_counters;
 
 typedef struct rt_scene_info {

@@ -202,6 +202,7 @@ int fetch_counters(rt_scene *s, cudaStream_t st) {
   c.box_tests = h[C_BOX]; c.tri_filter = h[C_TRI_FILTER]; c.tri_exact = h[C_TRI_EXACT];
   c.object_tests = h[C_OBJECT]; c.shaded_hits = h[C_SHADED]; c.texel_fetches = h[C_TEXEL];
   c.nodes_visited = h[C_NODES];
+  c.shadow_trivial = h[C_SHADOW_TRIVIAL];
   return RT_OK;
 }
 

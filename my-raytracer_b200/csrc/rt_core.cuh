@@ -460,6 +460,15 @@ template <bool COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold
         const D3 ldir = normalize(lv);
         const double ldist = norm(lv);
         bump<COUNT>(c, C_RAY_SHADOW);
+        // The reference casts this shadow ray (mytracer.cpp:589-599) and the ray count includes it, but when
+        // the surface faces away from the light (diff == 0, so spec = pow(0, shininess) = 0 for
+        // shininess > 0, mytracer.cpp:525-533) the light adds exactly 0 whether it is occluded or not:
+        // the result needs no traversal.
+        if (m.shininess > 0.0 && !(0.0 < dot(C.v(CD_N), ldir))) {
+          bump<COUNT>(c, C_SHADOW_TRIVIAL);
+          ++k;
+          continue;
+        }
         start_ray<COUNT>(c, H, C, add(P, scale(1e-4, ldir)), ldir, M_ANYHIT, ldist);
         break;
       }

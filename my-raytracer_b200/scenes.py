@@ -15,8 +15,10 @@ from .scene import MeshDesc, SceneDesc, material
 # --------------------------------------------------------------------------------------------
 
 
-def grid_quad(origin, eu, ev, nu, nv, with_uv=False):
-    """(nu x nv) quads -> 2*nu*nv triangles spanning origin + s*eu + t*ev, s,t in [0,1]."""
+def grid_quad(origin, eu, ev, nu, nv, with_uv=False, flip=False):
+    """(nu x nv) quads -> 2*nu*nv triangles spanning origin + s*eu + t*ev, s,t in [0,1].
+    Face normals (cross(p1 - p0, p2 - p0), mymesh.cpp:116) point along eu x ev, or ev x eu with flip=True:
+    the reference never turns a normal toward the viewer, so the winding decides which side is lit."""
     origin, eu, ev = (np.asarray(a, np.float64) for a in (origin, eu, ev))
     s = np.linspace(0.0, 1.0, nu + 1)
     t = np.linspace(0.0, 1.0, nv + 1)
@@ -28,6 +30,8 @@ def grid_quad(origin, eu, ev, nu, nv, with_uv=False):
     c = a + (nu + 1)
     d = c + 1
     idx = np.concatenate([np.stack([a, b, d], 1), np.stack([a, d, c], 1)], 0).astype(np.int32)
+    if flip:
+        idx = np.ascontiguousarray(idx[:, [0, 2, 1]])
     if with_uv:
         return pos, idx, S.reshape(-1).copy(), T.reshape(-1).copy()
     return pos, idx
@@ -74,9 +78,9 @@ def uv_sphere(center, radius, nslices, nstacks, with_uv=False, displace=None):
         for i in range(nslices):
             a, b, c, d = j * w + i, j * w + i + 1, (j + 1) * w + i, (j + 1) * w + i + 1
             if j != 0:
-                tris.append((a, d, b))
+                tris.append((a, b, d))          # outward-facing winding
             if j != nstacks - 1:
-                tris.append((a, c, d))
+                tris.append((a, d, c))
     idx = np.asarray(tris, np.int32)
     if with_uv:
         return pos, idx, (TH / (2.0 * np.pi)).reshape(-1).copy(), (1.0 - PH / np.pi).reshape(-1).copy()
@@ -227,9 +231,9 @@ def capsule_leg(base, radius, height, nseg, nstack):
     return pos, idx
 
 
-def wavy_sheet(origin, eu, ev, nu, nv, amp, fu, fv):
+def wavy_sheet(origin, eu, ev, nu, nv, amp, fu, fv, flip=False):
     """Height-field sheet: grid displaced along y by a sine product (no coplanar runs)."""
-    pos, idx = grid_quad(origin, eu, ev, nu, nv)
+    pos, idx = grid_quad(origin, eu, ev, nu, nv, flip=flip)
     s = np.linspace(0.0, 1.0, nu + 1)
     t = np.linspace(0.0, 1.0, nv + 1)
     S, T = np.meshgrid(s, t, indexing="xy")
@@ -268,13 +272,14 @@ def office(width=1920, height=1080, target_tris=34000, detail=1.0):
     carpet = material((0.15, 0.05, 0.05), (0.6, 0.2, 0.2), (0.02, 0.02, 0.02), 2.0, 0.0)
     X, Y, Z = 10.0, 3.0, 8.0   # room: x in [0,10], y in [0,3], z in [0,8]
     # room shell: 2 triangles per face, normals pointing inwards; floor separate (slightly mirroring)
-    add([grid_quad((0, 0, 0), (0, 0, Z), (0, Y, 0), 1, 1), grid_quad((X, 0, 0), (0, Y, 0), (0, 0, Z), 1, 1),
-         grid_quad((0, 0, 0), (0, Y, 0), (X, 0, 0), 1, 1), grid_quad((0, 0, Z), (X, 0, 0), (0, Y, 0), 1, 1),
-         grid_quad((0, Y, 0), (0, 0, Z), (X, 0, 0), 1, 1)], wall)
-    add(grid_quad((0, 0, 0), (X, 0, 0), (0, 0, Z), 2, 2), floor_m)
+    F = dict(flip=True)   # eu x ev points out of the room for these argument orders: flip towards the inside
+    add([grid_quad((0, 0, 0), (0, 0, Z), (0, Y, 0), 1, 1, **F), grid_quad((X, 0, 0), (0, Y, 0), (0, 0, Z), 1, 1, **F),
+         grid_quad((0, 0, 0), (0, Y, 0), (X, 0, 0), 1, 1, **F), grid_quad((0, 0, Z), (X, 0, 0), (0, Y, 0), 1, 1, **F),
+         grid_quad((0, Y, 0), (0, 0, Z), (X, 0, 0), 1, 1, **F)], wall)
+    add(grid_quad((0, 0, 0), (X, 0, 0), (0, 0, Z), 2, 2, **F), floor_m)
     # window pane on the z = 0 wall plus an exactly coplanar duplicate (equal-t tie-break exercise)
-    add([grid_quad((2.0, 1.0, 0.01), (0, 1.5, 0), (6.0, 0, 0), 1, 2),
-         grid_quad((2.0, 1.0, 0.01), (0, 1.5, 0), (3.0, 0, 0), 1, 1)], glass)
+    add([grid_quad((2.0, 1.0, 0.01), (0, 1.5, 0), (6.0, 0, 0), 1, 2, **F),
+         grid_quad((2.0, 1.0, 0.01), (0, 1.5, 0), (3.0, 0, 0), 1, 1, **F)], glass)
     # table: squashed ellipsoid top + 4 legs
     add(ellipsoid((5.0, 0.75, 4.2), (1.6, 0.05, 0.9), n(72), n(18)), wood, 1)
     add([capsule_leg((5.0 + sx * 1.0, 0.0, 4.2 + sz * 0.5), 0.04, 0.72, n(16), n(6))
@@ -333,10 +338,10 @@ def office(width=1920, height=1080, target_tris=34000, detail=1.0):
     q = rem // 2
     a = max(int(np.sqrt(q * 1.3)), 1)
     b = q // a
-    parts = [wavy_sheet((2.2, 0.012, 1.8), (5.6, 0, 0), (0, 0, 4.8), a, b, 0.006, 9.0, 7.0)]
+    parts = [wavy_sheet((2.2, 0.012, 1.8), (5.6, 0, 0), (0, 0, 4.8), a, b, 0.006, 9.0, 7.0, flip=True)]
     left = q - a * b
     if left:
-        parts.append(wavy_sheet((2.2, 0.012, 6.62), (5.6, 0, 0), (0, 0, 0.12), left, 1, 0.004, 5.0, 1.0))
+        parts.append(wavy_sheet((2.2, 0.012, 6.62), (5.6, 0, 0), (0, 0, 0.12), left, 1, 0.004, 5.0, 1.0, flip=True))
     add(parts, carpet)
     lights = [((5.0, 2.9, 4.0), (0.55, 0.55, 0.5)), ((2.0, 2.5, 6.5), (0.35, 0.35, 0.4)),
               ((8.0, 2.6, 1.5), (0.3, 0.3, 0.3))]
@@ -400,7 +405,7 @@ def textured(width=1920, height=1080, tex_size=1024, slices=224, stacks=112, see
         tex = value_noise_texture(tex_size, seed + bi, base=col, amp=0.6)
         meshes.append(MeshDesc(pos, idx, skin, 1, idx.copy(), u, v, tex))
     # ground: gently rolling height field (no coplanar runs, see office()), sky: one quad
-    pos, idx, u, v = grid_quad((-8, 0, -6), (16, 0, 0), (0, 0, 12), 64, 48, with_uv=True)
+    pos, idx, u, v = grid_quad((-8, 0, -6), (16, 0, 0), (0, 0, 12), 64, 48, with_uv=True, flip=True)
     pos = pos.copy()
     pos[:, 1] += 0.05 * np.sin(1.7 * pos[:, 0]) * np.cos(1.3 * pos[:, 2]) + 0.02 * np.sin(5.1 * pos[:, 0] + 3.3 * pos[:, 2])
     meshes.append(MeshDesc(pos, idx, material((0.2, 0.2, 0.2), (1, 1, 1), (0.1, 0.1, 0.1), 10.0, 0.0), 0, idx.copy(),
@@ -440,7 +445,7 @@ def scatter(width=3840, height=2160, n_objects=10000, slices=25, stacks=21, seed
             idx = (base_idx[None, :, :] + (np.arange(chunk.size) * nvb)[:, None, None]).reshape(-1, 3)
             c = cols[chunk[0]]
             meshes.append(MeshDesc(pos, idx, material(0.2 * c, c, (0.6, 0.6, 0.6), 60.0, mir), 1))
-    pos, idx = grid_quad((-80, 0, -80), (160, 0, 0), (0, 0, 120), 64, 64)
+    pos, idx = grid_quad((-80, 0, -80), (160, 0, 0), (0, 0, 120), 64, 64, flip=True)
     pos = pos.copy()
     pos[:, 1] += 0.3 * np.sin(0.11 * pos[:, 0]) * np.cos(0.13 * pos[:, 2]) + 0.1 * np.sin(0.7 * pos[:, 0] + 0.5 * pos[:, 2])
     meshes.append(MeshDesc(pos, idx, material((0.2, 0.2, 0.2), (0.5, 0.5, 0.5), (0.1, 0.1, 0.1), 10.0, 0.0), 0))

@@ -50,7 +50,7 @@ def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, 
     fo = capi.FrameOut(rgba.ctypes.data, px.ctypes.data, ids.ctypes.data if want_ids else None,
                        t.ctypes.data if want_ids else None)
     p = host.params(spp_grid=spp_grid, flags=flags, tile=tile)
-    cnt = (C.c_ulonglong * 10)()
+    cnt = (C.c_ulonglong * 16)()
     cost_n = np.zeros((H, W), np.uint32); cost_t = np.zeros((H, W), np.uint32)
     lp, lc = host.lights_pos, host.lights_color
     st = L.sim_render(buf, len(blob), C.byref(cam), lp.ctypes.data, lc.ctypes.data, lp.shape[0], C.byref(p),
@@ -58,7 +58,7 @@ def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, 
     if st != 0:
         raise RuntimeError("sim_render status %d: %s" % (st, L.sim_last_error().decode()))
     names = ("rays_primary", "rays_shadow", "rays_reflect", "box_tests", "tri_filter", "tri_exact", "object_tests",
-             "shaded_hits", "texel_fetches", "nodes_visited")
+             "shaded_hits", "texel_fetches", "nodes_visited", "shadow_trivial")
     out = dict(rgba8=rgba, pixels=px, hit_id=ids, hit_t=t, counters=dict(zip(names, [int(c) for c in cnt])))
     if cost:
         out["cost_nodes"], out["cost_tris"] = cost_n, cost_t
