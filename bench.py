@@ -6,10 +6,13 @@ Office-class scene (34 000 triangles, median-split BVH) at 1920x1080, 1 spp.
     python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU path (OpenMP)
 
 One "step" = one frame = one pass of the hot path over all pixels of the frame.
-  value      whole-job Mrays/s, scene/camera/lights resident in HBM, CUDA-event time of
-             [render kernel (+ NCCL frame gather for N > 1)], max over ranks
-  e2e        the same metric through the public C-ABI call rt_render with HOST buffers:
-             per step H2D of the lights + camera/params, kernel, D2H of the RGBA8 frame
+  value      whole-job Mrays/s, scene/camera/lights resident in HBM: K frames through the frame pipeline
+             (my-raytracer_b200/dist.py: one render-kernel launch per rank and frame, finished pixels stored
+             straight into rank 0's frame buffer over NVLink, 2 frames in flight), CUDA-event time from the
+             first launch to the last frame's completion signal, max over ranks
+  e2e        the same pipeline with HOST buffers: per step H2D of the lights from pinned memory, the C-ABI
+             call rt_render_device, D2H of the finished RGBA8 frame into pinned memory on rank 0
+             (e2e.sync: the synchronous rt_render call, one frame at a time, N = 1)
   roofline   FP32-issue roofline of the render kernel: algorithmic flops of the box /
              triangle / shading tests actually executed (instrumented launch, untimed) over the timed
              kernel duration, against 148 SMs x 128 lanes x 2 x sm_max_mhz
@@ -152,6 +155,25 @@ def run_reference(args):
     }))
 
 
+def l2_read_gbps(dev):
+    """Measured L2 read bandwidth: repeated reduction over a 48 MiB buffer that stays L2-resident (126 MB L2).
+    MEASURED_PEAKS.json has no L2 figure; the north star's roofline for an L2-resident scene needs one."""
+    import torch
+    x = torch.ones(48 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+    for _ in range(5):
+        x.sum()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 0.0
+    for _ in range(3):
+        a.record()
+        for _ in range(20):
+            x.sum()
+        b.record(); b.synchronize()
+        best = max(best, 20 * x.numel() * 4 / (a.elapsed_time(b) * 1e-3) / 1e9)
+    return best
+
+
 def run_b200(args):
     import numpy as np
     import torch
@@ -170,7 +192,8 @@ def run_b200(args):
     capi.check(lib.rt_init_device(local_rank), lib)
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)   # the per-frame signal must not queue
+        dist.init_process_group("nccl", device_id=dev, pg_options=opts)      # behind the persistent render grids
     desc = rt.scenes.office(width=args.width, height=args.height)
     W, H = args.width, args.height
 
@@ -191,27 +214,21 @@ def run_b200(args):
     info = scene.info()
     cam = host.camera
     chunk = int(os.environ.get("RT_TILE_CHUNK", "0")) or None
-    tile = rdist.tile_share(rank, world, chunk) if world > 1 else (0, 1, 1)
-    params = host.params(tile=tile)
-    d_lpos = torch.tensor(host.lights_pos, dtype=torch.float64, device=dev)
-    d_lcol = torch.tensor(host.lights_color, dtype=torch.float64, device=dev)
-    nl = d_lpos.shape[0]
-    d_rgba = torch.zeros(H * W * 4, dtype=torch.uint8, device=dev)
-    d_full = torch.zeros_like(d_rgba) if (world > 1 and rank == 0) else None
-    fo = capi.FrameOut(d_rgba.data_ptr(), None, None, None)
+    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "2"))
+    dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", "0.15"))
+    FLUSH = 160 * 1024 * 1024                                                   # > 126 MB L2
+    pipe = rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, tile_chunk=chunk,
+                               dyn_fraction=dyn_fraction, flush_bytes=FLUSH)
+    nl = pipe.nl
     stream = torch.cuda.current_stream()
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)       # > 126 MB L2
-
-    def frame():
-        capi.check(lib.rt_render_device(scene.handle, C.byref(cam), d_lpos.data_ptr(), d_lcol.data_ptr(), nl,
-                                        C.byref(params), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
-        if world > 1:
-            return rdist.gather_frame(d_rgba, d_full)
-        return d_rgba
 
     # ---- algorithmic work of one frame (instrumented launch, untimed; deterministic) -------------------
-    cparams = host.params(tile=tile, flags=capi.RT_FLAG_COUNTERS)
-    capi.check(lib.rt_render_device(scene.handle, C.byref(cam), d_lpos.data_ptr(), d_lcol.data_ptr(), nl,
+    # static-only partition here: the per-rank share of the dynamic tail varies from frame to frame, the sum
+    # over ranks does not
+    d_tmp = torch.zeros(H * W * 4, dtype=torch.uint8, device=dev)
+    fo = capi.FrameOut(d_tmp.data_ptr(), None, None, None)
+    cparams = host.params(tile=pipe.tile, flags=capi.RT_FLAG_COUNTERS)
+    capi.check(lib.rt_render_device(scene.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
                                     C.byref(cparams), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
     cnt = capi.Counters()
     capi.check(lib.rt_get_counters(scene.handle, C.byref(cnt)), lib)
@@ -222,81 +239,96 @@ def run_b200(args):
     tot = dict(zip(sorted(cnt), [int(v) for v in ct.tolist()]))
     rays_frame = tot["rays_primary"] + tot["rays_shadow"] + tot["rays_reflect"]
 
-    # ---- timed region: value --------------------------------------------------------------------------------
+    def timed(n_frames, host_io):
+        """n_frames through the pipeline; CUDA-event time from the first launch to the last frame's completion
+        signal, max over ranks."""
+        pipe.drain()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+        start = torch.cuda.Event(enable_timing=True)
+        start.record(pipe.compute[pipe.submitted % pipe.depth])
+        for _ in range(n_frames):
+            pipe.submit(host_io=host_io)
+        last = pipe.last_event
+        pipe.drain()
+        ms = start.elapsed_time(last)
+        return rdist.max_over_ranks(ms, dev) if world > 1 else ms
+
+    # ---- timed region: value (device-resident inputs, frames in flight) --------------------------------------
     for _ in range(max(args.warmup, 3)):
-        frame()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
+        pipe.submit()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kern_ms = []
-    torch.cuda.synchronize()
-    for a, b in evs:
-        flush.fill_(1)                                   # evict the scene from L2 between timed frames
-        a.record(stream)
-        frame()
-        b.record(stream)
-        b.synchronize()
-        kern_ms.append(scene.last_kernel_ms())
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
+    total_ms = timed(args.steps, host_io=False)
     clocks = sampler.result()
-    step_ms = [a.elapsed_time(b) for a, b in evs]
-    total_ms = sum(step_ms)
-    if world > 1:
-        total_ms = rdist.max_over_ranks(total_ms, dev)
     ms_per_step = total_ms / args.steps
     value = rays_frame / (ms_per_step * 1e-3) / 1e6
 
-    # ---- e2e: public C-ABI call with host buffers -----------------------------------------------------------
-    h_rgba = torch.zeros(H * W * 4, dtype=torch.uint8).pin_memory()
-    hfo = capi.FrameOut(h_rgba.data_ptr(), None, None, None)
-    lp = np.ascontiguousarray(host.lights_pos); lc = np.ascontiguousarray(host.lights_color)
-    eparams = host.params(tile=tile, flags=capi.RT_FLAG_NO_CLEAR)
-
-    def e2e_frame():
-        capi.check(lib.rt_render(scene.handle, C.byref(cam), lp.ctypes.data_as(capi.Vec4_p), lc.ctypes.data_as(capi.Vec4_p),
-                                 nl, C.byref(eparams), C.byref(hfo)), lib)
+    # ---- e2e: same pipeline with HOST buffers: H2D of the lights, kernel, D2H of the frame on rank 0 --------
     for _ in range(3):
-        e2e_frame()
-    if world > 1:
-        dist.barrier()
-    te = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_frame()
-    e2e_ms = (time.perf_counter() - te) * 1e3
-    if world > 1:
-        # host path at N > 1: each rank returns its own tiles to its own host buffer (no gather)
-        e2e_ms = rdist.max_over_ranks(e2e_ms, dev)
-    e2e_value = rays_frame / (e2e_ms / args.steps * 1e-3) / 1e6
+        pipe.submit(host_io=True)
+    e2e_total = timed(args.steps, host_io=True)
+    e2e_ms = e2e_total / args.steps
+    e2e_value = rays_frame / (e2e_ms * 1e-3) / 1e6
 
-    # ---- roofline of the render kernel --------------------------------------------------------------------
-    peaks = measured_peaks()
-    sm_max = float(peaks.get("sm_max_mhz", 1965.0))
-    peak_tflops = 148 * 128 * 2 * sm_max * 1e6 / 1e12
-    L = nl
-    flops = 24 * tot["box_tests"] + 48 * tot["tri_filter"] + (60 * L + 20) * tot["shaded_hits"]
-    alg_bytes = 32 * tot["box_tests"] + 48 * tot["tri_filter"] + 64 * tot["shaded_hits"] + 16 * tot["texel_fetches"] + 4 * W * H
-    kms_local = sum(kern_ms) / len(kern_ms)
-    kms = kms_local
+    # ---- one frame at a time (latency): serial launches, CUDA events around the kernel ---------------------
+    sparams = host.params(tile=pipe.tile, flags=capi.RT_FLAG_NO_CLEAR)
+    kern_ms = []
+    for i in range(8):
+        pipe.flush.fill_(1)
+        capi.check(lib.rt_render_device(scene.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
+                                        C.byref(sparams), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
+        kern_ms.append(scene.last_kernel_ms())
+    kms_local = sum(kern_ms[2:]) / len(kern_ms[2:])
     rank_ms = [kms_local]
     if world > 1:
-        kms = rdist.max_over_ranks(kms_local, dev)
         g = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
         dist.all_gather(g, torch.tensor([kms_local], dtype=torch.float64, device=dev))
         rank_ms = [float(x.item()) for x in g]
-    peak_tflops *= world                                  # whole-job flops against the N-GPU peak
-    achieved = flops / (kms * 1e-3) / 1e12
+    # the synchronous public call with host buffers (rt_render), one frame at a time, N = 1 only
+    sync_e2e = None
+    if world == 1:
+        h_rgba = torch.zeros(H * W * 4, dtype=torch.uint8).pin_memory()
+        hfo = capi.FrameOut(h_rgba.data_ptr(), None, None, None)
+        lp = np.ascontiguousarray(host.lights_pos); lc = np.ascontiguousarray(host.lights_color)
+        eparams = host.params(flags=capi.RT_FLAG_NO_CLEAR)
+        for i in range(3 + 10):
+            if i == 3:
+                te = time.perf_counter()
+            capi.check(lib.rt_render(scene.handle, C.byref(cam), lp.ctypes.data_as(capi.Vec4_p), lc.ctypes.data_as(capi.Vec4_p),
+                                     nl, C.byref(eparams), C.byref(hfo)), lib)
+        sync_ms = (time.perf_counter() - te) * 1e3 / 10
+        sync_e2e = {"value": rays_frame / (sync_ms * 1e-3) / 1e6, "ms_per_step": sync_ms, "api": "rt_render, one frame at a time"}
+
+    # ---- roofline of the render kernel (SURVEY 8d) -------------------------------------------------------------
+    peaks = measured_peaks()
+    sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+    peak_tflops = 148 * 128 * 2 * sm_max * 1e6 / 1e12 * world     # whole-job flops against the N-GPU peak
+    L = nl
+    flops = 24 * tot["box_tests"] + 48 * tot["tri_filter"] + (60 * L + 20) * tot["shaded_hits"]
+    alg_bytes = 32 * tot["box_tests"] + 48 * tot["tri_filter"] + 64 * tot["shaded_hits"] + 16 * tot["texel_fetches"] + 4 * W * H
+    achieved = flops / (ms_per_step * 1e-3) / 1e12
+    l2_bw = l2_read_gbps(dev) * world
+    t_fp32 = flops / (peak_tflops * 1e12)
+    t_l2 = alg_bytes / (l2_bw * 1e9)
     roof = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-            "kernel_ms_per_rank": rank_ms,
-            "traffic": None, "kernel": "rtb::render_kernel<false>", "kernel_ms": kms,
+            "traffic": None, "kernel": "rtb::render_kernel<false>",
+            "timed_over": "flops of one frame / ms_per_step of the timed region (kernels of successive frames overlap, "
+                          "so the per-launch duration is not the divisor; flush and launch gaps are inside)",
+            "kernel_ms_single_frame": max(rank_ms), "kernel_ms_per_rank": rank_ms,
             "peak_source": "148 SMs x 128 FP32 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json (FP32 is not in the "
                            "driver-measured set; the scene is L2-resident so HBM does not bound it)",
             "flops_per_launch": flops, "algorithmic_bytes_per_launch": alg_bytes,
-            "mem_GBps": alg_bytes / (kms * 1e-3) / 1e9, "hbm_peak_GBps": peaks.get("hbm_gbs")}
+            "mem_GBps": alg_bytes / (ms_per_step * 1e-3) / 1e9, "hbm_peak_GBps": peaks.get("hbm_gbs"),
+            "north_star": {"definition": "slower of FP32 peak for the counted intersection flops and L2 bandwidth for the "
+                                         "counted node/triangle bytes (scene resident in L2)",
+                           "l2_read_GBps_measured": l2_bw, "l2_how": "torch.sum over an L2-resident 48 MiB buffer, best of 3 x 20",
+                           "t_fp32_ms": t_fp32 * 1e3, "t_l2_ms": t_l2 * 1e3,
+                           "frac": max(t_fp32, t_l2) * 1e3 / ms_per_step,
+                           "note": "node/triangle bytes are served by L1 (96 % hits), so this fraction can exceed 1; "
+                                   "roofline.frac (FP32 issue) is the harder, reported bound"}}
 
     if rank == 0:
         line = {
@@ -304,16 +336,22 @@ def run_b200(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32 filter + f64 decide/shade", "data": "synthetic",
             "config": {"workload": WORKLOAD, "triangles": info["num_triangles"], "bvh_nodes": info["num_nodes_ref"],
-                       "lights": nl, "max_depth": desc.max_depth, "spp": 1, "l2": "flushed between timed frames (256 MiB fill)",
+                       "lights": nl, "max_depth": desc.max_depth, "spp": 1,
+                       "l2": "flushed before every timed frame (160 MiB fill on the frame's stream)",
+                       "frames_in_flight": pipe.depth,
                        "parallelism": f"tiles{world}" if world > 1 else "single",
-                       "tile_chunk": tile[2], "gather": "nccl reduce to rank 0" if world > 1 else "none"},
+                       "tile_chunk": pipe.tile[2], "dyn_tiles": pipe.dyn_tiles, "dyn_chunk": pipe.dyn_chunk,
+                       "gather": "fused: peer stores into rank 0's frame buffer over NVLink + 4-byte all-reduce signal"
+                                 if world > 1 else "none"},
             "mrays_primary": tot["rays_primary"] / (ms_per_step * 1e-3) / 1e6,
+            "latency_ms_single_frame": max(rank_ms),
             "rays_per_frame": {k: tot[k] for k in ("rays_primary", "rays_shadow", "rays_reflect")},
             "counters": tot,
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_ms / args.steps,
-                    "h2d_bytes_per_step": int(2 * nl * 32 + C.sizeof(capi.Camera) + C.sizeof(capi.RenderParams)),
-                    "d2h_bytes_per_step": W * H * 4, "api": "rt_render (host RGBA8 frame buffer, pinned)"},
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(2 * nl * 32) * world, "d2h_bytes_per_step": W * H * 4,
+                    "api": "rt_render_device per rank + pinned-host lights in / frame out on rank 0, frames in flight",
+                    "sync": sync_e2e},
             "gpu_launches": args.steps * world,
             "roofline": roof,
             "setup_ms": {"host_scene_build": host_ms, "flatten": info["flatten_ms"], "upload": info["upload_ms"],
@@ -322,6 +360,7 @@ def run_b200(args):
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = {k: v for k, v in cpu_leg(desc, args.cpu_seconds).items() if k not in ("seconds", "rays", "rows")}
         print(json.dumps(line))
+    pipe.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 1
+#define RT_B200_ABI_VERSION 2
 
 typedef enum rt_status {
   RT_OK = 0,
@@ -122,6 +122,12 @@ typedef struct rt_render_params {
    * renders tile t iff (t / tile_chunk) % tile_world == tile_rank.  1 GPU: world 1, rank 0. */
   int tile_rank, tile_world, tile_chunk;
   int flags;            /* RT_FLAG_* */
+  /* Cross-GPU dynamic tail queue (0 / NULL = off).  The LAST dyn_tiles tiles of the tile order are not
+   * statically owned: once a rank has drained its static share, its warps claim them dyn_chunk tiles at
+   * a time with a system-scope atomicAdd on *dyn_counter, a zero-initialised counter that every rank
+   * of the frame passes (rank 0's memory, peer-mapped on the others: rt_ipc_export / rt_ipc_open). */
+  int dyn_tiles, dyn_chunk;
+  unsigned long long *dyn_counter;
 } rt_render_params;
 
 #define RT_FLAG_EXACT_ONLY   1 /* validation: bypass the FP32 triangle filter (every test in FP64) */
@@ -197,6 +203,19 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_vec4 *lights_po
 int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_vec4 *d_lights_pos,
                      const rt_vec4 *d_lights_color, int num_lights, const rt_render_params *params,
                      const rt_frame_out *out_device, void *stream);
+/* ---- peer memory for the multi-GPU frame (one process per GPU) ---------------------------- */
+/* Device allocation that can be shared with the other ranks' processes (plain cudaMalloc, zero-filled):
+ * rank 0 allocates the frame buffer and the dynamic-queue counters, exports 64-byte handles, the host
+ * broadcasts them, every other rank opens them and passes the mapped pointers as rt_frame_out.rgba8 /
+ * rt_render_params.dyn_counter: finished pixels are then stored straight into rank 0's frame buffer over
+ * NVLink by the render kernel (no gather pass). */
+#define RT_IPC_HANDLE_BYTES 64
+int rt_shared_alloc(size_t bytes, void **dptr);
+int rt_shared_free(void *dptr);
+int rt_ipc_export(void *dptr, unsigned char handle[RT_IPC_HANDLE_BYTES]);
+int rt_ipc_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void **dptr);
+int rt_ipc_close(void *dptr);
+
 int rt_get_counters(const rt_scene *scene, rt_counters *out);
 /* CUDA-event time of the last rt_render / rt_render_device kernel on this scene (ms);
  * synchronises on the end event. */

@@ -82,7 +82,8 @@ class Camera(C.Structure):
 
 class RenderParams(C.Structure):
     _fields_ = [("background", Vec4), ("ambience", Vec4), ("max_depth", C.c_int), ("spp_grid", C.c_int),
-                ("tile_rank", C.c_int), ("tile_world", C.c_int), ("tile_chunk", C.c_int), ("flags", C.c_int)]
+                ("tile_rank", C.c_int), ("tile_world", C.c_int), ("tile_chunk", C.c_int), ("flags", C.c_int),
+                ("dyn_tiles", C.c_int), ("dyn_chunk", C.c_int), ("dyn_counter", C.c_void_p)]
 
 
 class FrameOut(C.Structure):
@@ -125,6 +126,11 @@ PROTOTYPES = {
                             C.POINTER(FrameOut)]),
     "rt_render_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_int,
                                    C.POINTER(RenderParams), C.POINTER(FrameOut), C.c_void_p]),
+    "rt_shared_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    "rt_shared_free": (C.c_int, [C.c_void_p]),
+    "rt_ipc_export": (C.c_int, [C.c_void_p, c_ubyte_p]),
+    "rt_ipc_open": (C.c_int, [c_ubyte_p, C.POINTER(C.c_void_p)]),
+    "rt_ipc_close": (C.c_int, [C.c_void_p]),
     "rt_get_counters": (C.c_int, [C.c_void_p, C.POINTER(Counters)]),
     "rt_last_kernel_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "rt_launch_compute_image": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Camera),
@@ -160,7 +166,7 @@ def load_library(path: str | None = None):
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.rt_abi_version() != 1:
+    if lib.rt_abi_version() != 2:
         raise RuntimeError("rt_b200 ABI version mismatch")
     if path is None:
         _lib = lib

@@ -42,8 +42,12 @@ struct rt_scene {
   unsigned long long *d_tex = nullptr;
   // per-frame device resources
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  unsigned long long *d_work = nullptr;
+  // Launch ring: frames may be in flight on several streams (one work counter + event pair per launch)
+  static constexpr int kRing = 8;
+  cudaEvent_t ev0[kRing] = {}, ev1[kRing] = {};
+  unsigned long long *d_work = nullptr; // kRing x {slot counter, pool-empty flag}
+  unsigned launch_seq = 0;
+  int last_slot = 0;
   unsigned long long *d_counters = nullptr;
   double *d_lights = nullptr; // pos[4*n] then col[4*n]
   int lights_cap = 0;
@@ -130,9 +134,11 @@ int adopt_blob(rt_scene *s) {
   }
   s->view.tex_objs = s->d_tex;
   RT_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-  RT_CUDA(cudaEventCreate(&s->ev0));
-  RT_CUDA(cudaEventCreate(&s->ev1));
-  RT_CUDA(cudaMalloc(&s->d_work, sizeof(unsigned long long)));
+  for (int k = 0; k < rt_scene::kRing; ++k) {
+    RT_CUDA(cudaEventCreate(&s->ev0[k]));
+    RT_CUDA(cudaEventCreate(&s->ev1[k]));
+  }
+  RT_CUDA(cudaMalloc(&s->d_work, sizeof(unsigned long long) * 2 * rt_scene::kRing));
   RT_CUDA(cudaMalloc(&s->d_counters, sizeof(unsigned long long) * C_COUNT));
   // persistent grid: SM count x resident CTAs of each kernel variant
   cudaDeviceProp prop;
@@ -164,19 +170,23 @@ int adopt_blob(rt_scene *s) {
 }
 
 int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const double *d_lcol, const FrameOut &out,
-           const int *d_list, int list_count, cudaStream_t st, const int *d_list_count = nullptr) {
+           const int *d_list, int list_count, cudaStream_t st, const int *d_list_count = nullptr,
+           unsigned long long *dyn_counter = nullptr) {
   KernelArgs a;
   a.sv = s->view; a.fp = fp;
   a.light_pos = d_lpos; a.light_col = d_lcol;
   a.out = out;
   a.pixel_list = d_list; a.list_count = list_count;
   a.list_count_ptr = d_list_count;
-  a.work_counter = s->d_work;
+  const int slot = (int)(s->launch_seq++ % rt_scene::kRing);
+  s->last_slot = slot;
+  a.work_counter = s->d_work + 2 * slot;
+  a.dyn_counter = (fp.static_tiles < fp.tiles_x * fp.tiles_y) ? dyn_counter : nullptr;
   a.counters = s->d_counters;
   a.scratch_d = s->d_scratch_d;
   a.scratch_i = s->d_scratch_i;
   const bool count = (fp.flags & RT_FLAG_COUNTERS) != 0;
-  RT_CUDA(cudaMemsetAsync(s->d_work, 0, sizeof(unsigned long long), st));
+  RT_CUDA(cudaMemsetAsync(a.work_counter, 0, 2 * sizeof(unsigned long long), st));
   if (count) RT_CUDA(cudaMemsetAsync(s->d_counters, 0, sizeof(unsigned long long) * C_COUNT, st));
 #ifdef RT_TAILPROBE
   {
@@ -184,11 +194,11 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
     RT_CUDA(cudaMemcpyAsync(s->d_counters, init, sizeof(init), cudaMemcpyHostToDevice, st));
   }
 #endif
-  RT_CUDA(cudaEventRecord(s->ev0, st));
+  RT_CUDA(cudaEventRecord(s->ev0[slot], st));
   if (count) render_kernel<true><<<s->grid_count, kBlockThreads, s->extra_smem, st>>>(a);
   else render_kernel<false><<<s->grid_plain, kBlockThreads, s->extra_smem, st>>>(a);
   RT_CUDA(cudaGetLastError());
-  RT_CUDA(cudaEventRecord(s->ev1, st));
+  RT_CUDA(cudaEventRecord(s->ev1[slot], st));
   s->timed = true;
   return RT_OK;
 }
@@ -278,8 +288,10 @@ int rt_scene_destroy(rt_scene *s) {
   auto F = [](void *p) { if (p) cudaFree(p); };
   F(s->d_blob); F(s->d_tex); F(s->d_work); F(s->d_counters); F(s->d_lights);
   F(s->d_scratch_d); F(s->d_scratch_i); F(s->d_rgba8); F(s->d_pixels); F(s->d_ids); F(s->d_t); F(s->d_list);
-  if (s->ev0) cudaEventDestroy(s->ev0);
-  if (s->ev1) cudaEventDestroy(s->ev1);
+  for (int k = 0; k < rt_scene::kRing; ++k) {
+    if (s->ev0[k]) cudaEventDestroy(s->ev0[k]);
+    if (s->ev1[k]) cudaEventDestroy(s->ev1[k]);
+  }
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
   return RT_OK;
@@ -324,7 +336,7 @@ int rt_render_device(rt_scene *s, const rt_camera *camera, const rt_vec4 *d_ligh
   fo.hit_id = out->hit_id; fo.hit_t = out->hit_t;
   cudaStream_t stx = static_cast<cudaStream_t>(stream);
   st = launch(s, fp, reinterpret_cast<const double *>(d_lights_pos), reinterpret_cast<const double *>(d_lights_color),
-              fo, nullptr, 0, stx);
+              fo, nullptr, 0, stx, nullptr, params->dyn_counter);
   if (st != RT_OK) return st;
 #ifdef RT_TAILPROBE
   return fetch_counters(s, stx);
@@ -378,7 +390,7 @@ int rt_render(rt_scene *s, const rt_camera *camera, const rt_vec4 *lights_pos, c
     fo.hit_t = s->d_t;
     if (partial) RT_CUDA(cudaMemsetAsync(s->d_t, 0, npx * 8, stx));
   }
-  st = launch(s, fp, s->d_lights, s->d_lights + 4 * (size_t)s->lights_cap, fo, nullptr, 0, stx);
+  st = launch(s, fp, s->d_lights, s->d_lights + 4 * (size_t)s->lights_cap, fo, nullptr, 0, stx, nullptr, params->dyn_counter);
   if (st != RT_OK) return st;
   if (out->rgba8) RT_CUDA(cudaMemcpyAsync(out->rgba8, s->d_rgba8, npx * 4, cudaMemcpyDeviceToHost, stx));
   if (out->pixels) RT_CUDA(cudaMemcpyAsync(out->pixels, s->d_pixels, npx * 32, cudaMemcpyDeviceToHost, stx));
@@ -392,6 +404,40 @@ int rt_render(rt_scene *s, const rt_camera *camera, const rt_vec4 *lights_pos, c
   return RT_OK;
 }
 
+int rt_shared_alloc(size_t bytes, void **dptr) {
+  if (!dptr || bytes == 0) { set_error("rt_shared_alloc: bad argument"); return RT_ERR_INVALID_ARG; }
+  std::string err;
+  int st = ensure_device(err);
+  if (st != RT_OK) { set_error(err); return st; }
+  RT_CUDA(cudaMalloc(dptr, bytes));   // a whole allocation of its own: cudaIpcGetMemHandle exports allocations
+  RT_CUDA(cudaMemset(*dptr, 0, bytes));
+  return RT_OK;
+}
+int rt_shared_free(void *dptr) {
+  if (dptr) RT_CUDA(cudaFree(dptr));
+  return RT_OK;
+}
+int rt_ipc_export(void *dptr, unsigned char handle[RT_IPC_HANDLE_BYTES]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "IPC handle size");
+  if (!dptr || !handle) { set_error("rt_ipc_export: null argument"); return RT_ERR_INVALID_ARG; }
+  cudaIpcMemHandle_t h;
+  RT_CUDA(cudaIpcGetMemHandle(&h, dptr));
+  std::memcpy(handle, &h, sizeof(h));
+  return RT_OK;
+}
+int rt_ipc_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void **dptr) {
+  if (!dptr || !handle) { set_error("rt_ipc_open: null argument"); return RT_ERR_INVALID_ARG; }
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, sizeof(h));
+  // maps the exporting rank's allocation into this process; peer access over NVLink is enabled lazily
+  RT_CUDA(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return RT_OK;
+}
+int rt_ipc_close(void *dptr) {
+  if (dptr) RT_CUDA(cudaIpcCloseMemHandle(dptr));
+  return RT_OK;
+}
+
 int rt_get_counters(const rt_scene *s, rt_counters *out) {
   if (!s || !out) { set_error("rt_get_counters: null argument"); return RT_ERR_INVALID_ARG; }
   *out = s->counters;
@@ -401,8 +447,8 @@ int rt_get_counters(const rt_scene *s, rt_counters *out) {
 int rt_last_kernel_ms(const rt_scene *s, float *ms) {
   if (!s || !ms) { set_error("rt_last_kernel_ms: null argument"); return RT_ERR_INVALID_ARG; }
   if (!s->timed) { set_error("rt_last_kernel_ms: nothing rendered yet"); return RT_ERR_INVALID_ARG; }
-  RT_CUDA(cudaEventSynchronize(s->ev1));
-  RT_CUDA(cudaEventElapsedTime(ms, s->ev0, s->ev1));
+  RT_CUDA(cudaEventSynchronize(s->ev1[s->last_slot]));
+  RT_CUDA(cudaEventElapsedTime(ms, s->ev0[s->last_slot], s->ev1[s->last_slot]));
   return RT_OK;
 }
 

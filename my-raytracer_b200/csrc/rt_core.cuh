@@ -519,19 +519,36 @@ RT_HD bool work_to_pixel(const Ctx &c, long long work, int &px, int &py) {
   const int l = (int)(work % (kTileW * kTileH));
   const long long chunk = fp.tile_chunk;
   const long long t = ((j / chunk) * fp.tile_world + fp.tile_rank) * chunk + (j % chunk);
-  const long long ntiles = (long long)fp.tiles_x * fp.tiles_y;
-  if (t >= ntiles) return false;
+  if (t >= fp.static_tiles) return false;
   const int tx = (int)(t % fp.tiles_x), ty = (int)(t / fp.tiles_x);
   px = tx * kTileW + (l % kTileW);
   py = ty * kTileH + (l / kTileW);
   return px < fp.cam.width && py < fp.cam.height;
 }
 
+// Dynamic pool: slot s of the pool covers tile static_tiles + s / 32, lane s % 32.
+RT_HD bool pool_to_pixel(const Ctx &c, long long s, int &px, int &py) {
+  const FrameParams &fp = c.fp;
+  const long long t = fp.static_tiles + s / (kTileW * kTileH);
+  const int l = (int)(s % (kTileW * kTileH));
+  if (t >= (long long)fp.tiles_x * fp.tiles_y) return false;
+  const int tx = (int)(t % fp.tiles_x), ty = (int)(t / fp.tiles_x);
+  px = tx * kTileW + (l % kTileW);
+  py = ty * kTileH + (l / kTileW);
+  return px < fp.cam.width && py < fp.cam.height;
+}
+RT_HD long long pool_chunks(const Ctx &c) {
+  const FrameParams &fp = c.fp;
+  if (c.pixel_list) return 0;
+  const long long dyn = (long long)fp.tiles_x * fp.tiles_y - fp.static_tiles;
+  return (dyn + fp.dyn_chunk - 1) / fp.dyn_chunk;
+}
+
 // number of work slots this rank must scan
 RT_HD long long work_slots(const Ctx &c) {
   const FrameParams &fp = c.fp;
   if (c.pixel_list) return c.list_count;
-  const long long ntiles = (long long)fp.tiles_x * fp.tiles_y;
+  const long long ntiles = fp.static_tiles;
   const long long group = (long long)fp.tile_chunk * fp.tile_world;
   const long long ngroups = (ntiles + group - 1) / group;
   return ngroups * fp.tile_chunk * (kTileW * kTileH);

@@ -35,6 +35,12 @@ inline int make_frame_params(const rt_camera *cam, int num_lights, const rt_rend
   fp.tiles_x = (cam->width + kTileW - 1) / kTileW;
   fp.tiles_y = (cam->height + kTileH - 1) / kTileH;
   fp.flags = p->flags;
+  const long long ntiles = (long long)fp.tiles_x * fp.tiles_y;
+  if (p->dyn_tiles < 0 || p->dyn_chunk < 0) { err = "render: negative dyn_tiles/dyn_chunk"; return RT_ERR_INVALID_ARG; }
+  if (p->dyn_tiles > 0 && (!p->dyn_counter || p->dyn_chunk < 1)) { err = "render: dyn_tiles needs dyn_counter and dyn_chunk >= 1"; return RT_ERR_INVALID_ARG; }
+  const long long dyn = p->dyn_tiles < ntiles ? p->dyn_tiles : ntiles;
+  fp.static_tiles = (int)(ntiles - dyn);
+  fp.dyn_chunk = p->dyn_chunk > 0 ? p->dyn_chunk : 1;
   return RT_OK;
 }
 

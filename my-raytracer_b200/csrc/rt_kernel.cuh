@@ -29,7 +29,8 @@ struct KernelArgs {
   const int *pixel_list;
   int list_count;
   const int *list_count_ptr;        // optional: list length produced on the device (no host sync)
-  unsigned long long *work_counter; // zeroed before every launch
+  unsigned long long *work_counter; // [0] local slot counter, [1] "dynamic pool is empty" flag; zeroed per launch
+  unsigned long long *dyn_counter;  // cross-GPU chunk counter of this frame (may be peer memory), or nullptr
   unsigned long long *counters;     // C_COUNT entries (COUNT builds)
   double *scratch_d;                // RT_COLD == 2: CD_NUM columns of grid*block doubles
   int *scratch_i;                   //               CI_NUM columns of grid*block ints
@@ -88,8 +89,11 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
   H.best_id = -1;
   H.xpar = 0;
   const long long slots = work_slots(c);
+  const long long nchunks = a.dyn_counter ? pool_chunks(c) : 0;
   const unsigned lane = threadIdx.x & 31u;
-  bool exhausted = false; // warp-uniform
+  bool exhausted = false;   // warp-uniform: no work left anywhere
+  bool local_done = false;  // warp-uniform: this rank's static share is drained
+  long long wp_next = 0, wp_end = 0; // warp-private range of dynamic-pool slots (warp-uniform)
 
   while (true) {
     // ---- phase A: path logic (FP64, cold state) for lanes whose traversal finished -----------
@@ -100,15 +104,45 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     if (idle != 0u && !exhausted) {
       const int n = __popc(idle);
       const int leader = __ffs(idle) - 1;
-      unsigned long long base = 0;
-      if ((int)lane == leader) base = atomicAdd(a.work_counter, (unsigned long long)n);
-      base = __shfl_sync(kFullMask, base, leader);
-      if ((long long)base >= slots) {
-        exhausted = true;
-      } else if (H.mode == M_IDLE) {
-        const long long mine = (long long)base + __popc(idle & ((1u << lane) - 1u));
-        int px, py;
-        if (mine < slots && work_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
+      const int rank_in_idle = __popc(idle & ((1u << lane) - 1u));
+      if (!local_done) {
+        // static share of this rank: one atomicAdd per refill, slots handed out by ballot rank
+        unsigned long long base = 0;
+        if ((int)lane == leader) base = atomicAdd(a.work_counter, (unsigned long long)n);
+        base = __shfl_sync(kFullMask, base, leader);
+        if ((long long)base >= slots) {
+          local_done = true;
+          exhausted = (nchunks == 0);
+        } else if (H.mode == M_IDLE) {
+          const long long mine = (long long)base + rank_in_idle;
+          int px, py;
+          if (mine < slots && work_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
+        }
+      } else {
+        // cross-GPU dynamic tail: the warp claims dyn_chunk tiles at a time with ONE system-scope atomic
+        // on the frame's shared counter and serves its lanes from that private range
+        if (wp_next >= wp_end) {
+          unsigned long long q = ~0ull;
+          if ((int)lane == leader) {
+            if (*(volatile unsigned long long *)(a.work_counter + 1) == 0ull) {
+              q = atomicAdd_system(a.dyn_counter, 1ull);
+              if ((long long)q >= nchunks) a.work_counter[1] = 1ull; // spare the other warps the remote atomic
+            }
+          }
+          q = __shfl_sync(kFullMask, q, leader);
+          if (q >= (unsigned long long)nchunks) {
+            exhausted = true;
+          } else {
+            wp_next = (long long)q * c.fp.dyn_chunk * (kTileW * kTileH);
+            wp_end = wp_next + (long long)c.fp.dyn_chunk * (kTileW * kTileH);
+          }
+        }
+        if (!exhausted) {
+          const long long mine = wp_next + rank_in_idle;
+          wp_next += n;
+          int px, py;
+          if (H.mode == M_IDLE && mine < wp_end && pool_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
+        }
       }
     }
     const unsigned busy = __ballot_sync(kFullMask, H.mode != M_IDLE);

@@ -142,6 +142,8 @@ struct FrameParams {
   int32_t tile_rank, tile_world, tile_chunk;
   int32_t tiles_x, tiles_y;
   int32_t flags;
+  int32_t static_tiles; // tiles [0, static_tiles) are statically sharded, [static_tiles, tiles_x*tiles_y) dynamic
+  int32_t dyn_chunk;    // tiles per claim from the dynamic pool
   int32_t pad;
 };
 

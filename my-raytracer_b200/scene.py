@@ -214,10 +214,12 @@ class HostScene:
         self.lights_pos = _vec4_array([l[0] for l in desc.lights]) if desc.lights else np.zeros((0, 4))
         self.lights_color = _vec4_array([l[1] for l in desc.lights]) if desc.lights else np.zeros((0, 4))
 
-    def params(self, spp_grid=1, flags=0, tile=(0, 1, 1), max_depth=None) -> RenderParams:
+    def params(self, spp_grid=1, flags=0, tile=(0, 1, 1), max_depth=None, dyn=(0, 0, None)) -> RenderParams:
+        """tile = (rank, world, chunk) static sharding; dyn = (dyn_tiles, dyn_chunk, counter device pointer):
+        the cross-GPU dynamic tail queue (include/rt_b200.h)."""
         d = self.desc
         return RenderParams(Vec4.of(d.background), Vec4.of(d.ambience), d.max_depth if max_depth is None else max_depth,
-                            spp_grid, tile[0], tile[1], tile[2], flags)
+                            spp_grid, tile[0], tile[1], tile[2], flags, int(dyn[0]), int(dyn[1]), dyn[2])
 
 
 class DeviceScene:

@@ -54,6 +54,11 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
   c.out.hit_id = out->hit_id;
   c.out.hit_t = out->hit_t;
   const long long slots = work_slots(c);
+  // dynamic tail queue: without a counter shared across processes the host build hands pool chunk q to
+  // rank q % world (any assignment that covers every chunk exactly once renders the same frame)
+  const long long nchunks = pool_chunks(c);
+  const long long chunk_slots = (long long)c.fp.dyn_chunk * (kTileW * kTileH);
+  const long long total_slots = slots + nchunks * chunk_slots;
   if (nthreads > 0) omp_set_num_threads(nthreads);
   std::vector<unsigned long long> total(C_COUNT, 0);
 #pragma omp parallel
@@ -69,9 +74,15 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
     Cd.db = cold_d;
     Cd.ib = cold_i;
 #pragma omp for schedule(dynamic, 256)
-    for (long long w = 0; w < slots; ++w) {
+    for (long long w = 0; w < total_slots; ++w) {
       int px, py;
-      if (!work_to_pixel(ct, w, px, py)) continue;
+      if (w < slots) {
+        if (!work_to_pixel(ct, w, px, py)) continue;
+      } else {
+        const long long s = w - slots;
+        if ((s / chunk_slots) % ct.fp.tile_world != ct.fp.tile_rank) continue;
+        if (!pool_to_pixel(ct, s, px, py)) continue;
+      }
       Hot H;
       H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.xpar = 0;
       begin_pixel<true>(ct, H, Cd, px, py);

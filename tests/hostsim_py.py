@@ -36,7 +36,7 @@ def flatten(host):
     return out
 
 
-def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, camera=None, cost=False):
+def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, camera=None, cost=False, dyn=(0, 0)):
     from my_raytracer_b200 import capi
     L = lib()
     blob = blob if blob is not None else flatten(host)
@@ -49,7 +49,9 @@ def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, 
     t = np.zeros((H, W))
     fo = capi.FrameOut(rgba.ctypes.data, px.ctypes.data, ids.ctypes.data if want_ids else None,
                        t.ctypes.data if want_ids else None)
-    p = host.params(spp_grid=spp_grid, flags=flags, tile=tile)
+    dummy = C.c_ulonglong(0)
+    p = host.params(spp_grid=spp_grid, flags=flags, tile=tile,
+                    dyn=(dyn[0], dyn[1], C.addressof(dummy) if dyn[0] else None))
     cnt = (C.c_ulonglong * 16)()
     cost_n = np.zeros((H, W), np.uint32); cost_t = np.zeros((H, W), np.uint32)
     lp, lc = host.lights_pos, host.lights_color

@@ -116,6 +116,49 @@ def test_blob_roundtrip_and_tile_sharding(rt, lib, gpu):
         assert (seen == 1).all() and np.array_equal(acc, full["rgba8"])
 
 
+def test_dynamic_tail_queue_and_shared_memory(rt, lib, gpu):
+    """Cross-GPU dynamic tail on one GPU: several 'ranks' render one after the other into ONE shared device
+    frame buffer (rt_shared_alloc, exported for IPC) and claim the last tiles from ONE shared counter.  Whoever
+    runs first drains the pool; the union must be the single-rank frame bit for bit, every pixel written once."""
+    import torch
+    host = rt.HostScene(rt.scenes.office(width=322, height=181), lib)
+    dev = rt.DeviceScene(host)
+    W, H = 322, 181
+    full = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(), want=("rgba8",))["rgba8"]
+    fb = C.c_void_p(); ctr = C.c_void_p()
+    gpu.check(lib.rt_shared_alloc(W * H * 4, C.byref(fb)), lib)
+    gpu.check(lib.rt_shared_alloc(64, C.byref(ctr)), lib)
+    handle = (C.c_ubyte * 64)()
+    gpu.check(lib.rt_ipc_export(fb, handle), lib)                  # what rank 0 would broadcast
+    assert any(handle)
+    d_lpos = torch.tensor(host.lights_pos, dtype=torch.float64, device="cuda")
+    d_lcol = torch.tensor(host.lights_color, dtype=torch.float64, device="cuda")
+    ntiles = ((W + 7) // 8) * ((H + 3) // 4)
+    from my_raytracer_b200 import dist as rdist
+    fbt = rdist.wrap_device_ptr(fb.value, W * H * 4)                # torch view of the shared allocation
+    for slot, (world, chunk, dyn_tiles, dyn_chunk) in enumerate(((2, 16, ntiles // 5, 8), (4, 3, ntiles, 1), (3, 5, 9, 64))):
+        fbt.zero_()
+        torch.cuda.synchronize()
+        fo = gpu.FrameOut(fb.value, None, None, None)
+        counter = ctr.value + 8 * slot                              # a fresh zero counter per frame
+        order = list(range(world))[::-1] if slot % 2 else list(range(world))
+        for r in order:
+            p = host.params(tile=(r, world, chunk), dyn=(dyn_tiles, dyn_chunk, counter), flags=gpu.RT_FLAG_NO_CLEAR)
+            gpu.check(lib.rt_render_device(dev.handle, C.byref(host.camera), d_lpos.data_ptr(), d_lcol.data_ptr(),
+                                           d_lpos.shape[0], C.byref(p), C.byref(fo), None), lib)
+        torch.cuda.synchronize()
+        got = fbt.cpu().numpy().reshape(H, W, 4)
+        assert np.array_equal(got, full)
+    # invalid dynamic-queue arguments are rejected
+    bad = host.params(dyn=(10, 4, None))
+    fo = gpu.FrameOut(fb.value, None, None, None)
+    assert lib.rt_render_device(dev.handle, C.byref(host.camera), d_lpos.data_ptr(), d_lcol.data_ptr(), d_lpos.shape[0],
+                                C.byref(bad), C.byref(fo), None) == gpu.RT_ERR_INVALID_ARG
+    del fbt
+    gpu.check(lib.rt_shared_free(fb), lib)
+    gpu.check(lib.rt_shared_free(ctr), lib)
+
+
 def test_full_size_properties(rt, lib, gpu, orc, oracle_kind):
     """BASELINE config 2 at full size (Office 34 k triangles, 1920x1080): determinism across launches,
     filter == exact-only, a checksum of the tile-sharded union, and oracle parity on a row sample."""

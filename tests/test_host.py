@@ -18,7 +18,7 @@ def test_cabi_exports_every_declared_symbol(rt, lib):
     assert declared == set(capi.PROTOTYPES), declared ^ set(capi.PROTOTYPES)
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.rt_abi_version() == 1
+    assert lib.rt_abi_version() == 2
 
 
 def test_struct_layouts_match_reference_headers(rt):
@@ -188,6 +188,17 @@ def test_tile_sharding_partitions_the_image(rt, lib, sim):
         acc = np.zeros_like(full["rgba8"]); seen = np.zeros(full["hit_id"].shape, int)
         for r in range(world):
             part = sim.render(host, blob, tile=(r, world, chunk))
+            mask = part["hit_id"] != -2
+            seen += mask
+            acc[mask] = part["rgba8"][mask]
+        assert (seen == 1).all()
+        assert np.array_equal(acc, full["rgba8"])
+    # with a dynamic tail: the last dyn_tiles tiles are claimed in chunks instead of being owned statically
+    ntiles = ((70 + 7) // 8) * ((45 + 3) // 4)
+    for world, chunk, dyn_tiles, dyn_chunk in ((2, 2, 30, 4), (3, 1, ntiles, 5), (4, 3, 7, 16), (2, 2, 10 ** 6, 1)):
+        acc = np.zeros_like(full["rgba8"]); seen = np.zeros(full["hit_id"].shape, int)
+        for r in range(world):
+            part = sim.render(host, blob, tile=(r, world, chunk), dyn=(dyn_tiles, dyn_chunk))
             mask = part["hit_id"] != -2
             seen += mask
             acc[mask] = part["rgba8"][mask]
