@@ -114,6 +114,30 @@ RT_HD I4 ld_i4(const void *p) {
 #endif
 }
 
+// 32-byte read-only load: sm_100 has 256-bit global loads (LDG.E.256), half the load instructions and L1
+// requests of two 16-byte loads for a 64-byte node record
+struct W8 {
+  unsigned w[8];
+};
+#ifndef RT_LD256
+#define RT_LD256 1
+#endif
+RT_HD W8 ld_w8(const void *p) {
+  W8 r;
+#if defined(__CUDA_ARCH__) && RT_LD256
+  asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
+      : "l"(p));
+#elif defined(__CUDA_ARCH__)
+  const uint4 a = __ldg(reinterpret_cast<const uint4 *>(p)), b = __ldg(reinterpret_cast<const uint4 *>(p) + 1);
+  r.w[0] = a.x; r.w[1] = a.y; r.w[2] = a.z; r.w[3] = a.w; r.w[4] = b.x; r.w[5] = b.y; r.w[6] = b.z; r.w[7] = b.w;
+#else
+  memcpy(&r, p, 32);
+#endif
+  return r;
+}
+RT_HD float w2f(unsigned u) { return __int_as_float_rt((int)u); }
+
 template <bool COUNT> RT_HD void bump(const Ctx &c, int which, unsigned n = 1) {
   if (COUNT) c.cnt[which] += n;
 }
@@ -239,13 +263,13 @@ struct alignas(8) StackEntry {
 // drift out of phase and ran 2x slower on B200 (profiles/r01_variants.md).
 template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   const char *np = reinterpret_cast<const char *>(c.sv.nodes) + (size_t)(unsigned)H.node * 64u;
-  const F4 q0 = ld_f4(np), q1 = ld_f4(np + 16), q2 = ld_f4(np + 32);
-  const I4 r = ld_i4(np + 48);
+  const W8 lo = ld_w8(np), hi = ld_w8(np + 32);   // two 32-byte loads per 64-byte record
+  I4 r; r.x = (int)hi.w[4]; r.y = (int)hi.w[5]; r.z = (int)hi.w[6]; r.w = (int)hi.w[7];
   bump<COUNT>(c, C_NODES);
   bump<COUNT>(c, C_BOX, 2);
-  // q0 = c0.ctr.xyz c0.half.x | q1 = c0.half.yz c1.ctr.xy | q2 = c1.ctr.z c1.half.xyz
-  const float b0c[3] = {q0.x, q0.y, q0.z}, b0h[3] = {q0.w, q1.x, q1.y};
-  const float b1c[3] = {q1.z, q1.w, q2.x}, b1h[3] = {q2.y, q2.z, q2.w};
+  // lo = c0.ctr.xyz c0.half.xyz c1.ctr.xy | hi = c1.ctr.z c1.half.xyz ref0 ref1 cnt0 cnt1
+  const float b0c[3] = {w2f(lo.w[0]), w2f(lo.w[1]), w2f(lo.w[2])}, b0h[3] = {w2f(lo.w[3]), w2f(lo.w[4]), w2f(lo.w[5])};
+  const float b1c[3] = {w2f(lo.w[6]), w2f(lo.w[7]), w2f(hi.w[0])}, b1h[3] = {w2f(hi.w[1]), w2f(hi.w[2]), w2f(hi.w[3])};
   float tn0, tn1;
   bool h0 = box_test(H.rf, b0c, b0h, H.thiS, tn0);
   bool h1 = box_test(H.rf, b1c, b1h, H.thiS, tn1);
