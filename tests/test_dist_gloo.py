@@ -26,7 +26,10 @@ def _worker(rank, world, port, q):
     blob = sim.flatten(host) if rank == 0 else None                            # ...but only rank 0 flattens it
     t = rdist.broadcast_blob(blob, "cpu")
     blob_r = bytes(t.numpy())
-    part = sim.render(host, blob_r, tile=rdist.tile_share(rank, world, 2))
+    # static chunked interleave + the dynamic tail (host build: pool chunk q goes to rank q % world)
+    dyn_tiles, dyn_chunk = rdist.dyn_split(90, 50, world, 0.3)
+    assert dyn_tiles > 0 and dyn_chunk > 0 and rdist.dyn_split(90, 50, 1) == (0, 0)
+    part = sim.render(host, blob_r, tile=rdist.tile_share(rank, world, 2), dyn=(dyn_tiles, dyn_chunk))
     local = torch.from_numpy(part["rgba8"].copy())
     full = rdist.gather_frame(local, torch.empty_like(local))
     ms = rdist.max_over_ranks(float(rank + 1), "cpu")
