@@ -236,6 +236,11 @@ int rt_launch_compute_image(rt_vec4 *d_pixels, rt_vec4 *d_tmpPixels, rt_vec4 *h_
  * pairwise child allocation; permutes data->normals_/vertexIdx_/textureIdx_ rows in place.
  * nodes: caller-allocated arrays of 2*N-1 entries.  nodes_used: out. */
 int rt_bvh_build_median(rt_data_soa *data, rt_bvh_nodes_soa *nodes, int *nodes_used);
+/* The same build on the GPU: level-synchronous, one segmented sort per level for the
+ * medians, the reference's in-place partition in closed form, nodes renumbered to the recursion's allocation
+ * order.  Same contract and bit-identical results (arrays, numbering, row permutation); host pointers in and
+ * out.  device_ms (may be NULL): CUDA-event time of the device part.  RT_ERR_NO_DEVICE without a GPU. */
+int rt_bvh_build_median_device(rt_data_soa *data, rt_bvh_nodes_soa *nodes, int *nodes_used, double *device_ms);
 /* Mesh::compute_normals (mymesh.cpp:103-163) for one mesh: face normals and angle-weighted
  * vertex normals.  pos/vnormals: nv vec4; idx: 3*nt local vertex ids; fnormals: nt vec4. */
 int rt_compute_normals(const rt_vec4 *pos, int nv, const int *idx, int nt, rt_vec4 *fnormals,

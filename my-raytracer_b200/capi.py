@@ -137,6 +137,7 @@ PROTOTYPES = {
                                           C.c_void_p, C.c_void_p, C.c_int, Vec4_p, Vec4_p, C.c_int,
                                           C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), C.POINTER(C.c_void_p)]),
     "rt_bvh_build_median": (C.c_int, [C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), c_int_p]),
+    "rt_bvh_build_median_device": (C.c_int, [C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), c_int_p, c_double_p]),
     "rt_compute_normals": (C.c_int, [Vec4_p, C.c_int, c_int_p, C.c_int, Vec4_p, Vec4_p]),
     "rt_camera_look_at": (C.c_int, [c_double_p, c_double_p, c_double_p, C.c_double, C.c_int, C.c_int,
                                     C.POINTER(Camera)]),

@@ -91,7 +91,8 @@ def look_at(cam: dict, lib=None) -> Camera:
 class HostScene:
     """Data SoA (mydata.h) + BVHNodes_SoA (mybvh.h) as numpy arrays, built like the reference does."""
 
-    def __init__(self, desc: SceneDesc, lib=None):
+    def __init__(self, desc: SceneDesc, lib=None, gpu_build=False):
+        """gpu_build: BVH through rt_bvh_build_median_device (same result, built on the GPU)."""
         self.lib = lib or capi.load_library()
         self.desc = desc
         lib = self.lib
@@ -195,7 +196,13 @@ class HostScene:
         if nt > 0:
             # remember the original row of every triangle through a tag carried in a copy of vertexIdx_
             orig_vidx = a["vertexIdx"].reshape(-1, 3).copy()
-            check(lib.rt_bvh_build_median(C.byref(d), C.byref(bv), C.byref(used)), lib)
+            self.bvh_device_ms = None
+            if gpu_build:
+                ms = C.c_double(0.0)
+                check(lib.rt_bvh_build_median_device(C.byref(d), C.byref(bv), C.byref(used), C.byref(ms)), lib)
+                self.bvh_device_ms = ms.value
+            else:
+                check(lib.rt_bvh_build_median(C.byref(d), C.byref(bv), C.byref(used)), lib)
             self._orig_vidx = orig_vidx
         self.nodes_used = used.value
         # analytic primitives

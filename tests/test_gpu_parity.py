@@ -159,6 +159,30 @@ def test_dynamic_tail_queue_and_shared_memory(rt, lib, gpu):
     gpu.check(lib.rt_shared_free(ctr), lib)
 
 
+def test_gpu_bvh_build_is_bit_identical_to_the_host_build(rt, lib, gpu):
+    """rt_bvh_build_median_device == rt_bvh_build_median (== BVH::initSoA, pinned against the reference sources in
+    tests/test_host.py): the five node arrays, the node numbering and the permuted triangle rows, on scenes with
+    duplicated centroids (unsplittable leaves), tiny meshes and the Office."""
+    dup = np.array([[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0.0]])
+    quad = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    cam = dict(eye=(0, 0, 5), center=(0, 0, 0), up=(0, 1, 0), fovy=40, width=8, height=8)
+    m = rt.material((1, 1, 1), (1, 1, 1), (0, 0, 0), 1.0)
+    descs = [rt.scenes.office(width=16, height=9), rt.scenes.mixed_small(width=16, height=9),
+             rt.scenes.rings(width=16, height=9, nu=64, nv=16), rt.scenes.scatter(width=16, height=9, n_objects=30),
+             rt.SceneDesc("dups", [rt.MeshDesc(dup, np.concatenate([quad] * 9, 0), m)], [], [((0, 0, 5), (1, 1, 1))], cam),
+             rt.SceneDesc("one", [rt.MeshDesc(dup, quad[:1], m)], [], [((0, 0, 5), (1, 1, 1))], cam),
+             rt.SceneDesc("three", [rt.MeshDesc(dup, np.concatenate([quad, quad[:1]], 0), m)], [], [((0, 0, 5), (1, 1, 1))], cam)]
+    for d in descs:
+        a = rt.HostScene(d, lib)
+        b = rt.HostScene(d, lib, gpu_build=True)
+        assert a.nodes_used == b.nodes_used and b.bvh_device_ms is not None
+        n = a.nodes_used
+        for k in ("left", "first", "count", "bbmin", "bbmax"):
+            assert np.array_equal(a.bvh_arrays[k][:max(n, 1)], b.bvh_arrays[k][:max(n, 1)]), (d.name, k)
+        for k in ("vertexIdx", "textureIdx", "normals"):
+            assert np.array_equal(a.arrays[k], b.arrays[k], equal_nan=(k == "normals")), (d.name, k)   # degenerate faces: NaN normals
+
+
 def test_full_size_properties(rt, lib, gpu, orc, oracle_kind):
     """BASELINE config 2 at full size (Office 34 k triangles, 1920x1080): determinism across launches,
     filter == exact-only, a checksum of the tile-sharded union, and oracle parity on a row sample."""
