@@ -182,16 +182,22 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   H.found = 0;
   H.sp = 0;
   double best = tmax;
+  float othi = thi_of(best);
+  const bool exact_only = (c.fp.flags & 1) != 0;
   const SceneView &sv = c.sv;
   for (int k = 0; k < sv.num_objects; ++k) {
     const ObjectRec &ob = sv.objects[k];
     double t;
     bump<COUNT>(c, C_OBJECT);
+    // FP32 pre-filter (a 4-wide batched variant of this loop was measured and is slower: 4.6 vs 3.2 ms on the
+    // molecule scene, the loop is latency-bound at 250 k pixels, not throughput-bound)
+    if (ob.kind == 0 && !exact_only && !sphere_filter(H.rf, ob.cf, ob.rf, ob.cabs, othi)) continue;
     const bool hit = (ob.kind == 0) ? sphere_exact(o, d, ld3(ob.center), ob.radius, t)
                                     : plane_exact(o, d, ld3(ob.center), ld3(ob.normal), t);
     if (hit && t < best) {
       if (mode == M_ANYHIT) { H.found = 1; H.node = -1; C.d(CD_BEST_T) = best; return; }
       best = t;
+      othi = thi_of(best);
       H.best_id = sv.num_tris + k;
     }
   }

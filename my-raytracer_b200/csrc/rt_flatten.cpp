@@ -291,6 +291,9 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     r.specular[0] = o.material.specular.x; r.specular[1] = o.material.specular.y; r.specular[2] = o.material.specular.z;
     r.shininess = o.material.shininess;
     r.mirror = o.material.mirror;
+    for (int a = 0; a < 3; ++a) r.cf[a] = (float)r.center[a];
+    r.rf = (float)o.radius;
+    r.cabs = round_up(std::fabs(r.center[0]) + std::fabs(r.center[1]) + std::fabs(r.center[2]));
   }
 
   // ---- 4. assemble -----------------------------------------------------------------------------

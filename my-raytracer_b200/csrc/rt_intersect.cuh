@@ -136,6 +136,29 @@ RT_HD bool tri_exact(const D3 &o, const D3 &d, const D3 &p0, const D3 &p1, const
   return true;
 }
 
+// Conservative FP32 pre-filter of Sphere::intersect: false only if the exact test certainly misses, certainly has
+// both roots behind the origin, or certainly yields t > thi.  The reference tests every analytic primitive for
+// every ray (linear list, no BVH over Raytracer::objects_): for the molecule scene that is 600 FP64 quadratic
+// solves (sqrt + 2 divisions) per ray; the filter replaces most of them by 12 FP32 operations.
+// Error bounds: delta bounds the absolute error of each component of oc = o - c computed from FP32-rounded
+// operands; E bounds the error of disc = (d.oc)^2 - |oc|^2 + r^2; St the error of a root.
+RT_HD bool sphere_filter(const RayF &r, const float *cf, float rf, float cabs, float thi) {
+  const float ocx = r.ox - cf[0], ocy = r.oy - cf[1], ocz = r.oz - cf[2];
+  const float oc2 = fmaf(ocx, ocx, fmaf(ocy, ocy, ocz * ocz));
+  const float bh = fmaf(r.dx, ocx, fmaf(r.dy, ocy, r.dz * ocz));
+  const float r2 = rf * rf;
+  const float disc = fmaf(bh, bh, r2 - oc2);
+  const float delta = 8.0f * kU32 * (r.o1n + cabs) + FLT_MIN;
+  const float ocn = sqrtf(oc2) + 2.0f * delta;
+  const float E = 64.0f * kU32 * (oc2 + r2) + 8.0f * ocn * delta + FLT_MIN;
+  if (disc < -E) return false;
+  const float sq = sqrtf(fmaxf(disc + E, 0.0f));
+  const float St = 4.0f * delta + 8.0f * kU32 * ocn + 32.0f * kU32 * (fabsf(bh) + sq) + FLT_MIN;
+  if (-bh + sq + St < 0.0f) return false; // both roots behind the origin (the exact test needs t > 1e-5)
+  if (-bh - sq - St > thi) return false;  // even the nearer root lies beyond the best distance
+  return true;
+}
+
 // == Plane::intersect (myplane.cpp:22-49)
 RT_HD bool plane_exact(const D3 &o, const D3 &d, const D3 &center, const D3 &n, double &t_out) {
   const double cosTheta = dot(n, d);

@@ -18,7 +18,7 @@
 //             survivors; the confirmation reproduces the reference arithmetic bit for bit.
 // * TriShade 128 B: normals (face or 3 vertex normals), UVs, mesh id — read once per shaded hit.
 // * MeshRec  128 B: material + draw mode + texture descriptor (mydata.h:57-71).
-// * ObjectRec: analytic primitives (Raytracer::objects_), FP64.
+// * ObjectRec 176 B: analytic primitives (Raytracer::objects_), FP64, + FP32 operands of the sphere pre-filter.
 // * NodeMaxX  16 B: the FP64 bb_max_.x of both children, read ONLY by rays whose direction.x is exactly
 //             0: the reference's slab test (mybvh.cpp:99-135) computes (bb_max.x - o.x)/0 = 0/0 = NaN when
 //             o.x == bb_max.x, the NaN survives std::min and the box is REJECTED (with its subtree).
@@ -32,7 +32,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 4;
+constexpr uint32_t kBlobVersion = 5;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -87,9 +87,12 @@ struct alignas(16) ObjectRec {
   double radius;
   double ambient[3], diffuse[3], specular[3];
   double shininess, mirror;
-  double pad;
+  // FP32 operands of the conservative sphere pre-filter (rt_intersect.cuh sphere_filter)
+  float cf[3], rf;   // centre and radius rounded to FP32
+  float cabs;        // |cx| + |cy| + |cz| (error bound)
+  float padf;
 };
-static_assert(sizeof(ObjectRec) == 160, "ObjectRec must be 160 bytes");
+static_assert(sizeof(ObjectRec) == 176, "ObjectRec must be 176 bytes");
 
 struct alignas(16) NodeMaxX {
   double c0_max_x, c1_max_x;

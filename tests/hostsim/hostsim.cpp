@@ -131,6 +131,18 @@ int sim_tri_exact(const double *p0, const double *p1, const double *p2, const do
   return hit ? 1 : 0;
 }
 
+// conservative FP32 sphere pre-filter, operands rounded exactly like the flattener does
+int sim_sphere_filter(const double *center, double radius, const double *o, const double *d, double thi) {
+  using namespace rtb;
+  float cf[3];
+  for (int k = 0; k < 3; ++k) cf[k] = (float)center[k];
+  const double ca = std::fabs(center[0]) + std::fabs(center[1]) + std::fabs(center[2]);
+  float cabs = (float)ca; if ((double)cabs < ca) cabs = nextafterf(cabs, INFINITY);
+  RayF r;
+  rayf_setup(r, ld3(o), ld3(d), 0.0f);
+  return sphere_filter(r, cf, (float)radius, cabs, thi_of(thi)) ? 1 : 0;
+}
+
 // conservative FP32 box test against an FP64 box, encoded in centre/half-extent form by the flattener
 // (a one-triangle-pair scene would do the same; this calls the flattener's arithmetic through a tiny BVH)
 int sim_box_test(const double *bmin, const double *bmax, const double *o, const double *d, double thi,

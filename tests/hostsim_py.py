@@ -81,6 +81,12 @@ def tri_exact(p0, p1, p2, o, d):
     return bool(hit), out
 
 
+def sphere_filter(center, radius, o, d, thi):
+    L = lib()
+    L.sim_sphere_filter.argtypes = [_dp, C.c_double, _dp, _dp, C.c_double]
+    return bool(L.sim_sphere_filter(_v(center), float(radius), _v(o), _v(d), float(thi)))
+
+
 def box_test(bmin, bmax, o, d, thi, extent_scale=1.0):
     """extent_scale > 1 emulates a box that is small against the scene's box_extent (larger slack)."""
     return bool(lib().sim_box_test(_v(bmin), _v(bmax), _v(o), _v(d), float(thi), float(extent_scale)))

@@ -88,6 +88,39 @@ def test_tri_filter_is_conservative(sim, orc, oracle_kind):
     assert misses > 100 and passed_miss < 0.25 * misses   # and it is a useful filter, not a pass-through
 
 
+def test_sphere_filter_is_conservative(sim, orc, oracle_kind):
+    """Property: whenever the oracle's sphere test hits at parameter t, the FP32 pre-filter passes for every
+    thi >= t (grazing rays, origins inside / on the sphere, far-away origins), and it rejects most clear misses."""
+    rng = np.random.default_rng(21)
+    hits = misses = rejected = 0
+    for i in range(12000):
+        s = 10.0 ** rng.uniform(-2, 2)
+        c = rng.uniform(-1, 1, 3) * s * 5
+        rad = s * 10.0 ** rng.uniform(-2, 0.3)
+        o = c + rng.normal(size=3) * rad * 10.0 ** rng.uniform(-1, 1.5)
+        if i % 5 == 0:                                   # grazing: aim at a point on the silhouette
+            n = np.cross(rng.normal(size=3), o - c); n /= np.linalg.norm(n)
+            tgt = c + n * rad * (1.0 + rng.choice([-1e-7, 0.0, 1e-7, -1e-3, 1e-3]))
+        else:
+            tgt = c + rng.normal(size=3) * rad * rng.uniform(0, 2.0)
+        d = tgt - o
+        if i % 7 == 0:
+            d[rng.integers(0, 3)] = 0.0
+        if not d.any():
+            continue
+        d /= np.linalg.norm(d)
+        hit, out7 = orc.sphere_test(c, rad, o, d, kind=oracle_kind)
+        t = out7[0]
+        if hit:
+            hits += 1
+            assert sim.sphere_filter(c, rad, o, d, t * (1 + 1e-12)), (i, c, rad, o, d, t)
+            assert sim.sphere_filter(c, rad, o, d, 1e300)
+        else:
+            misses += 1
+            rejected += not sim.sphere_filter(c, rad, o, d, 1e300)
+    assert hits > 3000 and misses > 2000 and rejected > 0.9 * misses
+
+
 def test_box_test_is_conservative(sim, orc, oracle_kind):
     """Property: whenever the reference slab test accepts a box, the FP32 test on the outward-rounded box
     does too (for thi = +inf), including axis-parallel rays and flat boxes."""
