@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--topology", default="sah", choices=["sah", "reference"],
+                    help="tree ordinary rays walk: the library's SAH tree (default) or the reference's median-split topology")
+    ap.add_argument("--no-ab", action="store_true", help="skip the A/B frame on the other tree")
     return ap.parse_args()
 
 
@@ -197,19 +200,20 @@ def run_b200(args):
     desc = rt.scenes.office(width=args.width, height=args.height)
     W, H = args.width, args.height
 
+    scene_flags = capi.RT_SCENE_REFERENCE_TOPOLOGY if args.topology == "reference" else 0
     # ---- scene: rank 0 builds + flattens, one broadcast replicates the blob -----------------------------
     t0 = time.perf_counter()
     host = rt.HostScene(desc, lib)                       # every rank needs camera/lights; cheap (34 k tris)
     host_ms = (time.perf_counter() - t0) * 1e3
     if world > 1:
-        blob = rt.DeviceScene(host).export_blob() if rank == 0 else None
+        blob = rt.DeviceScene(host, scene_flags=scene_flags).export_blob() if rank == 0 else None
         tb = time.perf_counter()
         t_blob = rdist.broadcast_blob(blob, dev)
         torch.cuda.synchronize()
         bcast_ms = (time.perf_counter() - tb) * 1e3
         scene = rt.DeviceScene(lib=lib, blob_device_ptr=t_blob.data_ptr(), blob_bytes=t_blob.numel())
     else:
-        scene = rt.DeviceScene(host)
+        scene = rt.DeviceScene(host, scene_flags=scene_flags)
         bcast_ms = 0.0
     info = scene.info()
     cam = host.camera
@@ -302,6 +306,23 @@ def run_b200(args):
         sync_ms = (time.perf_counter() - te) * 1e3 / 10
         sync_e2e = {"value": rays_frame / (sync_ms * 1e-3) / 1e6, "ms_per_step": sync_ms, "api": "rt_render, one frame at a time"}
 
+    # ---- A/B: the same frame with every ray on the reference's median-split topology (N = 1, serial frames) ----
+    other_tree = None
+    if world == 1 and not args.no_ab:
+        other_flags = 0 if scene_flags else capi.RT_SCENE_REFERENCE_TOPOLOGY
+        sc2 = rt.DeviceScene(host, scene_flags=other_flags)
+        ms2 = []
+        for i in range(8):
+            pipe.flush.fill_(1)
+            capi.check(lib.rt_render_device(sc2.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
+                                            C.byref(sparams), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
+            ms2.append(sc2.last_kernel_ms())
+        k2 = sum(ms2[2:]) / len(ms2[2:])
+        other_tree = {"traversal_tree": "sah" if scene_flags else "reference", "kernel_ms_single_frame": k2,
+                      "mrays": rays_frame / (k2 * 1e-3) / 1e6,
+                      "note": "same frame bit for bit (tests/test_gpu_parity.py); compare with latency_ms_single_frame"}
+        sc2.close()
+
     # ---- roofline of the render kernel -------------------------------------------------------------
     peaks = measured_peaks()
     sm_max = float(peaks.get("sm_max_mhz", 1965.0))
@@ -336,6 +357,9 @@ def run_b200(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32 filter + f64 decide/shade", "data": "synthetic",
             "config": {"workload": WORKLOAD, "triangles": info["num_triangles"], "bvh_nodes": info["num_nodes_ref"],
+                       "traversal_tree": ("reference median-split topology" if info["topology"] == 1 else
+                                          "library-built SAH tree over the same triangles; reference tree kept for d.x == 0 rays"),
+                       "traversal_records": info["num_nodes_traversal"],
                        "lights": nl, "max_depth": desc.max_depth, "spp": 1,
                        "l2": "flushed before every timed frame (160 MiB fill on the frame's stream)",
                        "frames_in_flight": pipe.depth,
@@ -345,6 +369,7 @@ def run_b200(args):
                                  if world > 1 else "none"},
             "mrays_primary": tot["rays_primary"] / (ms_per_step * 1e-3) / 1e6,
             "latency_ms_single_frame": max(rank_ms),
+            "other_tree": other_tree,
             "rays_per_frame": {k: tot[k] for k in ("rays_primary", "rays_shadow", "rays_reflect")},
             "counters": tot,
             "clocks": clocks,

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 2
+#define RT_B200_ABI_VERSION 3
 
 typedef enum rt_status {
   RT_OK = 0,
@@ -159,11 +159,13 @@ typedef struct rt_counters {
 typedef struct rt_scene_info {
   int num_triangles, num_meshes, num_objects;
   int num_nodes_ref;       /* nodes reachable from the root in the reference layout */
-  int num_nodes_flat;      /* 64-byte two-child records */
+  int num_nodes_flat;      /* 64-byte two-child records (both trees) */
   int max_depth_bvh;
   int max_leaf_size;
   size_t blob_bytes;       /* flattened scene in HBM */
   double flatten_ms, upload_ms;
+  int topology;            /* 0: SAH traversal tree + reference tree for d.x == 0 rays; 1: reference tree only */
+  int num_nodes_traversal; /* records of the tree ordinary rays walk */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene;
@@ -180,6 +182,15 @@ int rt_abi_version(void);
  * shading records, texture objects; uploads one contiguous blob.  objects may be NULL. */
 int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
                     int num_objects, rt_scene **out);
+/* Same with options.  By default the flattener ALSO builds its own surface-area-heuristic tree over the
+ * same triangles and ordinary rays walk that one: hits are decided by the bit-exact FP64 test and ties by the
+ * reference's primitive index (the BVH-order row of Data), so the frame does not depend on the tree — except
+ * for rays with direction.x == 0 exactly, which keep walking the reference's tree because its slab test
+ * (mybvh.cpp:99-135) rejects boxes through a 0/0 there.  RT_SCENE_REFERENCE_TOPOLOGY keeps every ray on the
+ * reference's median-split topology (mybvh.cpp:438-472). */
+#define RT_SCENE_REFERENCE_TOPOLOGY 1u
+int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
+                       int num_objects, unsigned scene_flags, rt_scene **out);
 int rt_scene_destroy(rt_scene *scene);
 int rt_scene_get_info(const rt_scene *scene, rt_scene_info *out);
 

@@ -16,6 +16,7 @@ RT_OK = 0
 RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_BAD_SCENE, RT_ERR_LIMIT, RT_ERR_OOM = 1, 2, 3, 4, 5, 6
 RT_SPHERE, RT_PLANE = 0, 1
 RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR = 1, 2, 4
+RT_SCENE_REFERENCE_TOPOLOGY = 1
 
 c_int_p = C.POINTER(C.c_int)
 c_double_p = C.POINTER(C.c_double)
@@ -103,7 +104,7 @@ class SceneInfo(C.Structure):
     _fields_ = [("num_triangles", C.c_int), ("num_meshes", C.c_int), ("num_objects", C.c_int),
                 ("num_nodes_ref", C.c_int), ("num_nodes_flat", C.c_int), ("max_depth_bvh", C.c_int),
                 ("max_leaf_size", C.c_int), ("blob_bytes", C.c_size_t), ("flatten_ms", C.c_double),
-                ("upload_ms", C.c_double)]
+                ("upload_ms", C.c_double), ("topology", C.c_int), ("num_nodes_traversal", C.c_int)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -116,6 +117,8 @@ PROTOTYPES = {
     "rt_abi_version": (C.c_int, []),
     "rt_scene_create": (C.c_int, [C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), C.POINTER(Object), C.c_int,
                                   C.POINTER(C.c_void_p)]),
+    "rt_scene_create_ex": (C.c_int, [C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), C.POINTER(Object), C.c_int, C.c_uint,
+                                     C.POINTER(C.c_void_p)]),
     "rt_scene_destroy": (C.c_int, [C.c_void_p]),
     "rt_scene_get_info": (C.c_int, [C.c_void_p, C.POINTER(SceneInfo)]),
     "rt_scene_blob_size": (C.c_int, [C.c_void_p, c_size_p]),
@@ -167,7 +170,7 @@ def load_library(path: str | None = None):
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.rt_abi_version() != 2:
+    if lib.rt_abi_version() != 3:
         raise RuntimeError("rt_b200 ABI version mismatch")
     if path is None:
         _lib = lib

@@ -107,6 +107,9 @@ int adopt_blob(rt_scene *s) {
   s->view.num_meshes = h.num_meshes; s->view.num_objects = h.num_objects;
   s->view.box_extent = h.box_extent;
   s->view.maxx = reinterpret_cast<const NodeMaxX *>(b + h.off_maxx);
+  s->view.tri_id = reinterpret_cast<const int32_t *>(b + h.off_tri_id);
+  s->view.tri_pos = reinterpret_cast<const int32_t *>(b + h.off_tri_pos);
+  s->view.q_base = h.q_base;
   s->view.root_max_x = h.root_max_x;
   // texture objects over the blob's texel section ("textures go through texture objects")
   std::vector<MeshRec> meshes(h.num_meshes);
@@ -165,6 +168,8 @@ int adopt_blob(rt_scene *s) {
   s->info.num_triangles = h.num_tris; s->info.num_meshes = h.num_meshes; s->info.num_objects = h.num_objects;
   s->info.num_nodes_ref = h.num_nodes_ref; s->info.num_nodes_flat = h.num_nodes;
   s->info.max_depth_bvh = h.max_depth; s->info.max_leaf_size = h.max_leaf; s->info.blob_bytes = s->bytes;
+  s->info.topology = h.topology;
+  s->info.num_nodes_traversal = h.topology == 0 ? h.q_base : h.num_nodes;
   std::memset(&s->counters, 0, sizeof(s->counters));
   return RT_OK;
 }
@@ -268,13 +273,22 @@ int rt_scene_create_from_blob(const void *blob, size_t bytes, int is_device, rt_
 
 int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
                     int num_objects, rt_scene **out) {
+  // RT_B200_TOPOLOGY=reference: A/B switch for callers that cannot pass flags (the drop-in launcher)
+  unsigned flags = 0;
+  if (const char *e = std::getenv("RT_B200_TOPOLOGY"))
+    if (std::strcmp(e, "reference") == 0) flags |= RT_SCENE_REFERENCE_TOPOLOGY;
+  return rt_scene_create_ex(data, bvh, objects, num_objects, flags, out);
+}
+
+int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
+                       int num_objects, unsigned scene_flags, rt_scene **out) {
   if (!out) { set_error("rt_scene_create: null out"); return RT_ERR_INVALID_ARG; }
   std::string err;
   int st = ensure_device(err);
   if (st != RT_OK) { set_error(err); return st; }
   const auto t0 = std::chrono::steady_clock::now();
   std::vector<unsigned char> blob;
-  st = flatten_scene(data, bvh, objects, num_objects, blob, err);
+  st = flatten_scene(data, bvh, objects, num_objects, scene_flags, blob, err);
   if (st != RT_OK) { set_error(err); return st; }
   const double flat_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   st = rt_scene_create_from_blob(blob.data(), blob.size(), 0, out);

@@ -204,16 +204,19 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   C.d(CD_BEST_T) = best;
   H.thi = thi_of(best);
   H.thiS = this_of(H.thi);
-  H.node = (sv.num_nodes > 0) ? 0 : -1;
   H.xpar = (d.x == 0.0);
+  // ordinary rays walk the traversal tree (records from 0), rays with d.x == 0 the reference's own tree
+  // (records from q_base; the same tree when q_base == 0): only there does the 0/0 slab quirk apply
+  H.node = (sv.num_nodes > 0) ? (H.xpar ? sv.q_base : 0) : -1;
   // root box, tested on entry by the reference (mybvh.cpp:157): (bb_max.x - o.x)/0 = NaN rejects it
   if (H.xpar && o.x == sv.root_max_x) H.node = -1;
 }
 
 // FP64 confirmation of one filter survivor + nearest / any-hit bookkeeping.  Rare (~0.7 per ray).
-template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const Cold<S> &C, int i) {
+// j: position in traversal order (TriExact index); the reported / tie-breaking id is tri_id[j].
+template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const Cold<S> &C, int j) {
   bump<COUNT>(c, C_TRI_EXACT);
-  const TriExact &e = c.sv.exact[i];
+  const TriExact &e = c.sv.exact[j];
   TriHit h;
   if (!tri_exact(C.v(CD_O), C.v(CD_D), ld3(e.p0), ld3(e.p1), ld3(e.p2), h)) return;
   const double best = C.d(CD_BEST_T);
@@ -225,6 +228,7 @@ template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const 
   // strict '<' keeps the first hit in DFS order (mybvh.cpp:169); leaves are visited in ascending
   // triangle index there, so "lower index wins a tie" is visit-order independent.  Analytic
   // primitives are tested before the BVH, so they win ties against triangles.
+  const int i = c.sv.tri_id[j];
   const bool better = (h.t < best) || (h.t == best && H.best_id >= 0 && H.best_id < c.sv.num_tris && i < H.best_id);
   if (better) {
     C.d(CD_BEST_T) = h.t;
@@ -235,11 +239,15 @@ template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const 
 }
 
 // Triangles [first, last) of one leaf — or of two sibling leaves, whose ranges are adjacent (rt_types.h).
+// Leaves of the traversal tree hold positions of the triangle records; leaves of the reference tree (walked
+// by d.x == 0 rays only) hold reference primitive indices, mapped through tri_pos.
 template <bool COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last) {
   const bool exact_only = (c.fp.flags & 1) != 0;
-  for (int i = first; i < last; ++i) {
+  for (int k = first; k < last; ++k) {
     bump<COUNT>(c, C_TRI_FILTER);
     bool pass = exact_only;
+    int i = k;
+    if (H.xpar) i = c.sv.tri_pos[k];
     if (!exact_only) {
       const char *p = reinterpret_cast<const char *>(c.sv.filt + i);
       const F4 a = ld_f4(p), b = ld_f4(p + 16), d = ld_f4(p + 32);
@@ -280,7 +288,7 @@ template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Co
   bool h0 = box_test(H.rf, b0c, b0h, H.thiS, tn0);
   bool h1 = box_test(H.rf, b1c, b1h, H.thiS, tn1);
   if (H.xpar) { // rare (exactly axis-parallel rays): reproduce the reference's NaN rejection
-    const NodeMaxX mx = c.sv.maxx[H.node];
+    const NodeMaxX mx = c.sv.maxx[H.node - c.sv.q_base];
     const double ox = C.d(CD_O);
     h0 = h0 && !(ox == mx.c0_max_x);
     h1 = h1 && !(ox == mx.c1_max_x);
@@ -390,7 +398,7 @@ template <bool COUNT, int S> RT_HD void hit_setup(const Ctx &c, Hot &H, const Co
   int mat;
   if (H.best_id < sv.num_tris) {
     const int i = H.best_id;
-    const TriExact &e = sv.exact[i];
+    const TriExact &e = sv.exact[sv.tri_pos[i]];
     TriHit h;
     h.t = best; h.alpha = 0.0; h.beta = 0.0; h.gamma = 0.0;
     tri_exact(o, d, ld3(e.p0), ld3(e.p1), ld3(e.p2), h); // same arithmetic as the accepted test

@@ -7,6 +7,7 @@
 // as is: one 64-byte NodeRec per interior node, children in the reference's left/right order,
 // leaves referencing the same [firstTriIdx_, firstTriIdx_+triCount_) ranges.
 #include "rt_flatten.h"
+#include "rt_sah.h"
 #include <cmath>
 #include <cstring>
 #include <initializer_list>
@@ -36,7 +37,7 @@ struct Walk {
 } // namespace
 
 int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
-                  int num_objects, std::vector<unsigned char> &blob, std::string &err) {
+                  int num_objects, unsigned flags, std::vector<unsigned char> &blob, std::string &err) {
   if (num_objects < 0 || (num_objects > 0 && !objects)) {
     err = "flatten: objects pointer/count invalid";
     return RT_ERR_INVALID_ARG;
@@ -70,9 +71,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   const int cap = 2 * N - 1; // slots the reference allocates (mybvh.cpp:386)
   double box_extent = 0.0;
   // centre / half-extent form, outward: [ctr - half, ctr + half] (as real numbers) contains the FP64 box
-  auto box_of = [&](int r, float *ctr, float *half) {
-    const rt_vec4 &a = bvh->bb_min_[r], &b = bvh->bb_max_[r];
-    const double lo[3] = {a.x, a.y, a.z}, hi[3] = {b.x, b.y, b.z};
+  auto box_lohi = [&](const double *lo, const double *hi, float *ctr, float *half) {
     for (int k = 0; k < 3; ++k) {
       const float c = (float)(0.5 * (lo[k] + hi[k]));
       const double need = std::fmax(hi[k] - (double)c, (double)c - lo[k]); // each difference: one FP64 rounding
@@ -82,6 +81,11 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
       const double e = std::fabs((double)c) + (double)h;
       if (e > box_extent) box_extent = e;
     }
+  };
+  auto box_of = [&](int r, float *ctr, float *half) {
+    const rt_vec4 &a = bvh->bb_min_[r], &b = bvh->bb_max_[r];
+    const double lo[3] = {a.x, a.y, a.z}, hi[3] = {b.x, b.y, b.z};
+    box_lohi(lo, hi, ctr, half);
   };
   auto leaf_ok = [&](int r) -> bool {
     const int f = bvh->firstTriIdx_[r], c = bvh->triCount_[r];
@@ -245,6 +249,77 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     for (TriFilter &f : filt) f.k_det = std::numeric_limits<float>::infinity();
   }
 
+  // ---- 2b. the traversal tree (rt_sah.h): SAH over the same triangles, reference tree kept for the quirk ----
+  std::vector<int> tri_id(N), tri_pos(N);
+  for (int i = 0; i < N; ++i) tri_id[i] = tri_pos[i] = i;
+  int q_base = 0, topology = 1;
+  const int num_nodes_q = (int)nodes.size();
+  if (!(flags & RT_SCENE_REFERENCE_TOPOLOGY) && N > 2 && !root_is_leaf) {
+    std::vector<float> plo(3 * (size_t)N), phi(3 * (size_t)N);
+    for (int i = 0; i < N; ++i) {
+      const TriExact &e = exact[i];
+      for (int k = 0; k < 3; ++k) {
+        plo[3 * (size_t)i + k] = round_down(std::fmin(e.p0[k], std::fmin(e.p1[k], e.p2[k])));
+        phi[3 * (size_t)i + k] = round_up(std::fmax(e.p0[k], std::fmax(e.p1[k], e.p2[k])));
+      }
+    }
+    std::vector<int> order;
+    std::vector<SahNode> sn;
+    int sah_depth = 0;
+    build_sah(plo.data(), phi.data(), N, order, sn, sah_depth);
+    if (!sn.empty() && sn[0].count == 0 && sah_depth <= kStackMax) {
+      // interior nodes in DFS pre-order, as for the reference tree
+      std::vector<NodeRec> trav;
+      std::vector<Walk> todo;
+      trav.emplace_back();
+      todo.push_back({0, 0, 1});
+      while (!todo.empty()) {
+        const Walk w = todo.back();
+        todo.pop_back();
+        const SahNode &sp = sn[w.ref_node];
+        const int ch[2] = {sp.left, sp.right};
+        NodeRec n;
+        int ref[2], cnt[2], child_flat[2] = {-1, -1};
+        for (int s2 = 0; s2 < 2; ++s2) {
+          const SahNode &cn = sn[ch[s2]];
+          const double lo[3] = {cn.lo[0], cn.lo[1], cn.lo[2]}, hi[3] = {cn.hi[0], cn.hi[1], cn.hi[2]};
+          box_lohi(lo, hi, s2 ? n.c1_ctr : n.c0_ctr, s2 ? n.c1_half : n.c0_half);
+          if (cn.count > 0) {
+            ref[s2] = cn.first; cnt[s2] = cn.count;
+            if (cn.count > max_leaf) max_leaf = cn.count;
+          } else {
+            child_flat[s2] = (int)trav.size();
+            trav.emplace_back();
+            ref[s2] = child_flat[s2]; cnt[s2] = 0;
+          }
+        }
+        if (child_flat[1] >= 0) todo.push_back({ch[1], child_flat[1], w.depth + 1});
+        if (child_flat[0] >= 0) todo.push_back({ch[0], child_flat[0], w.depth + 1});
+        n.ref0 = ref[0]; n.cnt0 = cnt[0]; n.ref1 = ref[1]; n.cnt1 = cnt[1];
+        trav[w.flat_idx] = n;
+      }
+      if (sah_depth > max_depth) max_depth = sah_depth;
+      q_base = (int)trav.size();
+      topology = 0;
+      for (NodeRec &r : nodes) { // reference tree: interior child references move behind the traversal tree
+        if (r.cnt0 == 0) r.ref0 += q_base;
+        if (r.cnt1 == 0 && r.c1_half[0] >= 0.0f) r.ref1 += q_base;
+      }
+      trav.insert(trav.end(), nodes.begin(), nodes.end());
+      nodes.swap(trav);
+      // triangle records into traversal order
+      std::vector<TriFilter> f2(N);
+      std::vector<TriExact> e2(N);
+      for (int j = 0; j < N; ++j) {
+        const int i = order[j];
+        tri_id[j] = i; tri_pos[i] = j;
+        f2[j] = filt[i]; e2[j] = exact[i];
+      }
+      filt.swap(f2);
+      exact.swap(e2);
+    }
+  }
+
   // ---- 3. meshes, objects, texels ------------------------------------------------------------
   std::vector<MeshRec> meshes(num_meshes);
   size_t num_texels = 0;
@@ -314,6 +389,9 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.off_objects = off; off = align_up(off + objs.size() * sizeof(ObjectRec), kSectionAlign);
   h.off_texels = off;  off = align_up(off + num_texels * 4 * sizeof(float), kSectionAlign);
   h.off_maxx = off;    off = align_up(off + maxx.size() * sizeof(NodeMaxX), kSectionAlign);
+  h.off_tri_id = off;  off = align_up(off + tri_id.size() * sizeof(int32_t), kSectionAlign);
+  h.off_tri_pos = off; off = align_up(off + tri_pos.size() * sizeof(int32_t), kSectionAlign);
+  h.q_base = q_base; h.num_nodes_q = num_nodes_q; h.topology = topology;
   h.root_max_x = N > 0 ? bvh->bb_max_[0].x : 0.0;
   h.total_bytes = off;
   blob.assign(off, 0);
@@ -324,6 +402,8 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     std::memcpy(blob.data() + h.off_filter, filt.data(), filt.size() * sizeof(TriFilter));
     std::memcpy(blob.data() + h.off_exact, exact.data(), exact.size() * sizeof(TriExact));
     std::memcpy(blob.data() + h.off_shade, shade.data(), shade.size() * sizeof(TriShade));
+    std::memcpy(blob.data() + h.off_tri_id, tri_id.data(), tri_id.size() * sizeof(int32_t));
+    std::memcpy(blob.data() + h.off_tri_pos, tri_pos.data(), tri_pos.size() * sizeof(int32_t));
   }
   if (num_meshes > 0) std::memcpy(blob.data() + h.off_meshes, meshes.data(), meshes.size() * sizeof(MeshRec));
   if (num_objects > 0) std::memcpy(blob.data() + h.off_objects, objs.data(), objs.size() * sizeof(ObjectRec));
@@ -348,7 +428,10 @@ int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
                   h.off_meshes + (size_t)h.num_meshes * sizeof(MeshRec) <= h.off_objects &&
                   h.off_objects + (size_t)h.num_objects * sizeof(ObjectRec) <= h.off_texels &&
                   h.off_texels + h.num_texels * 16 <= h.off_maxx &&
-                  h.off_maxx + (size_t)h.num_nodes * sizeof(NodeMaxX) <= h.total_bytes;
+                  h.off_maxx + (size_t)h.num_nodes_q * sizeof(NodeMaxX) <= h.off_tri_id &&
+                  h.off_tri_id + (size_t)h.num_tris * sizeof(int32_t) <= h.off_tri_pos &&
+                  h.off_tri_pos + (size_t)h.num_tris * sizeof(int32_t) <= h.total_bytes &&
+                  h.q_base >= 0 && h.num_nodes_q >= 0 && (size_t)h.q_base + (size_t)h.num_nodes_q == (size_t)h.num_nodes;
   if (!ok) { err = "blob: section table inconsistent"; return RT_ERR_BAD_SCENE; }
   return RT_OK;
 }
@@ -368,7 +451,9 @@ SceneView view_of_blob(const unsigned char *blob) {
   v.maxx = reinterpret_cast<const NodeMaxX *>(blob + h.off_maxx);
   v.root_max_x = h.root_max_x;
   v.num_nodes = h.num_nodes; v.num_tris = h.num_tris; v.num_meshes = h.num_meshes; v.num_objects = h.num_objects;
-  v.box_extent = h.box_extent; v.pad = 0;
+  v.tri_id = reinterpret_cast<const int32_t *>(blob + h.off_tri_id);
+  v.tri_pos = reinterpret_cast<const int32_t *>(blob + h.off_tri_pos);
+  v.box_extent = h.box_extent; v.q_base = h.q_base;
   return v;
 }
 

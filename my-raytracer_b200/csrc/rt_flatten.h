@@ -8,9 +8,9 @@
 
 namespace rtb {
 
-// Returns RT_OK or an rt_status; on failure `err` holds the message.
+// Returns RT_OK or an rt_status; on failure `err` holds the message.  flags: RT_SCENE_* (rt_b200.h).
 int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
-                  int num_objects, std::vector<unsigned char> &blob, std::string &err);
+                  int num_objects, unsigned flags, std::vector<unsigned char> &blob, std::string &err);
 
 // Validates a blob received from another rank (magic, version, section bounds).
 int check_blob(const unsigned char *blob, size_t bytes, std::string &err);

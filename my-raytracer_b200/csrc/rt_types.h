@@ -4,9 +4,17 @@
 // One contiguous, 512-byte-sectioned blob (so it can be broadcast with a single NCCL call):
 //
 //   BlobHeader | NodeRec[] | TriFilter[] | TriExact[] | TriShade[] | MeshRec[] | ObjectRec[] | texels | NodeMaxX[]
+//              | tri_id[] | tri_pos[]
 //
-// * NodeRec   64 B  (4 x float4): one record per INTERIOR node of the reference's median-split
-//             tree (mybvh.h:49-55 / mybvh.cpp:438-472) holding BOTH child boxes in FP32
+// Two trees share the NodeRec array (rt_sah.h): records [0, q_base) are the product's SAH traversal tree,
+// records [q_base, q_base + num_nodes_q) the reference's median-split tree, walked only by rays with
+// direction.x == 0 (NodeMaxX below).  With RT_SCENE_REFERENCE_TOPOLOGY there is one tree (q_base == 0) and
+// every ray walks the reference topology.  TriFilter / TriExact are stored in the leaf order of the traversal
+// tree; tri_id[position] is the reference's primitive index (the BVH-order row of Data, which is what the
+// path reports and breaks ties with), tri_pos[] its inverse; TriShade stays in reference order.
+//
+// * NodeRec   64 B  (4 x float4): one record per INTERIOR node of a binary tree (the reference's:
+//             mybvh.h:49-55 / mybvh.cpp:438-472) holding BOTH child boxes in FP32
 //             centre / half-extent form (outward-rounded: [c-h, c+h] contains the FP64 box),
 //             plus the two child references.  Same topology, half the dependent loads of the
 //             reference's 76 B/node five-array layout; the centre/half form turns the slab test
@@ -32,7 +40,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 5;
+constexpr uint32_t kBlobVersion = 6;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -109,9 +117,14 @@ struct BlobHeader {
   float scene_extent; // max |coordinate| over all vertices (diagnostics)
   float box_extent;   // >= |ctr| + half of every child box, every axis (slab-test error bound)
   float pad_f[2];
-  uint64_t off_maxx;   // NodeMaxX[num_nodes]
+  uint64_t off_maxx;   // NodeMaxX[num_nodes_q], indexed by (record - q_base)
   double root_max_x;   // bb_max_.x of reference node 0 (tested on entry, mybvh.cpp:157)
-  uint64_t reserved[4];
+  uint64_t off_tri_id, off_tri_pos; // int32[num_tris] each
+  int32_t q_base;      // first record of the reference-topology tree (0: it IS the traversal tree)
+  int32_t num_nodes_q; // its record count; num_nodes = total records of both trees
+  int32_t topology;    // 0 SAH traversal tree + reference tree, 1 reference tree only
+  int32_t pad_i;
+  uint64_t reserved[2];
 };
 static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
 
@@ -126,10 +139,12 @@ struct SceneView {
   const float *texels; // 4 floats per texel (host/test build); the kernel uses tex_objs instead
   const unsigned long long *tex_objs; // cudaTextureObject_t per mesh (0 when untextured)
   const NodeMaxX *maxx;
+  const int32_t *tri_id;  // traversal-order position -> reference primitive index
+  const int32_t *tri_pos; // reference primitive index -> traversal-order position
   double root_max_x;
   int32_t num_nodes, num_tris, num_meshes, num_objects;
   float box_extent;
-  int32_t pad;
+  int32_t q_base;
 };
 
 struct CameraRec {

@@ -232,13 +232,16 @@ class HostScene:
 class DeviceScene:
     """Flattened scene resident in HBM + render entry points (host-buffer path)."""
 
-    def __init__(self, host: HostScene = None, lib=None, blob: bytes | None = None, blob_device_ptr=None, blob_bytes=0):
+    def __init__(self, host: HostScene = None, lib=None, blob: bytes | None = None, blob_device_ptr=None, blob_bytes=0,
+                 scene_flags=0):
+        """scene_flags: capi.RT_SCENE_REFERENCE_TOPOLOGY keeps every ray on the reference's median-split tree
+        (default: ordinary rays walk the library's own SAH tree; same frame either way)."""
         self.lib = lib or (host.lib if host is not None else capi.load_library())
         self.host = host
         h = C.c_void_p()
         if host is not None:
-            check(self.lib.rt_scene_create(C.byref(host.data), C.byref(host.bvh), host.objects, host.num_objects,
-                                           C.byref(h)), self.lib)
+            check(self.lib.rt_scene_create_ex(C.byref(host.data), C.byref(host.bvh), host.objects, host.num_objects,
+                                              int(scene_flags), C.byref(h)), self.lib)
         elif blob is not None:
             buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
             check(self.lib.rt_scene_create_from_blob(buf, len(blob), 0, C.byref(h)), self.lib)

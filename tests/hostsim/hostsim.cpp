@@ -22,10 +22,10 @@ extern "C" {
 const char *sim_last_error(void) { return rtb::g_err.c_str(); }
 
 int sim_flatten(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects, int nobj,
-                unsigned char **blob_out, size_t *bytes) {
+                unsigned flags, unsigned char **blob_out, size_t *bytes) {
   std::vector<unsigned char> blob;
   std::string err;
-  const int st = rtb::flatten_scene(data, bvh, objects, nobj, blob, err);
+  const int st = rtb::flatten_scene(data, bvh, objects, nobj, flags, blob, err);
   if (st != RT_OK) { rtb::set_error(err); return st; }
   *blob_out = (unsigned char *)std::malloc(blob.size());
   std::memcpy(*blob_out, blob.data(), blob.size());

@@ -23,12 +23,14 @@ def lib():
     return _lib
 
 
-def flatten(host):
-    """HostScene -> bytes of the flattened blob (same flattener the CUDA library uses)."""
+def flatten(host, scene_flags=0):
+    """HostScene -> bytes of the flattened blob (same flattener the CUDA library uses).
+    scene_flags: capi.RT_SCENE_REFERENCE_TOPOLOGY keeps every ray on the reference's tree."""
     L = lib()
     blob = C.POINTER(C.c_ubyte)()
     n = C.c_size_t()
-    st = L.sim_flatten(C.byref(host.data), C.byref(host.bvh), host.objects, host.num_objects, C.byref(blob), C.byref(n))
+    st = L.sim_flatten(C.byref(host.data), C.byref(host.bvh), host.objects, host.num_objects,
+                       C.c_uint(scene_flags), C.byref(blob), C.byref(n))
     if st != 0:
         raise RuntimeError("flatten status %d: %s" % (st, L.sim_last_error().decode()))
     out = C.string_at(blob, n.value)

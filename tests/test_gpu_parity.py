@@ -55,6 +55,29 @@ def test_live_oracle_scenes(rt, lib, gpu, orc, oracle_kind, name, kw):
     _check(out, ref["ids"], ref["t"], rt.quantize_rgb8(ref["rgb"]), ref["rgb"])
 
 
+@pytest.mark.parametrize("name,kw", [
+    ("office", dict(width=480, height=270)),
+    ("scatter", dict(width=256, height=144, n_objects=300)),      # has a column of d.x == 0 rays (NaN quirk path)
+    ("textured", dict(width=256, height=144, tex_size=256, slices=64, stacks=32)),
+    ("mixed_small", dict(width=333, height=201, seed=9)),
+])
+def test_frame_does_not_depend_on_the_tree(rt, lib, gpu, name, kw):
+    """Library-built SAH traversal tree (default) vs every ray on the reference's median-split topology:
+    bit-identical ids, distances and FP64 pixels, fewer node visits."""
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    sah = rt.DeviceScene(host)
+    ref = rt.DeviceScene(host, scene_flags=gpu.RT_SCENE_REFERENCE_TOPOLOGY)
+    assert sah.info()["topology"] == 0 and ref.info()["topology"] == 1
+    p = host.params(flags=gpu.RT_FLAG_COUNTERS)
+    a = sah.render(host.camera, host.lights_pos, host.lights_color, p)
+    b = ref.render(host.camera, host.lights_pos, host.lights_color, p)
+    for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+        assert np.array_equal(a[k], b[k]), k
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits"):
+        assert a["counters"][k] == b["counters"][k]
+    assert a["counters"]["nodes_visited"] < b["counters"]["nodes_visited"]
+
+
 def test_supersampling_grid(rt, lib, gpu):
     g = np.load(os.path.join(GOLDEN, "scene_mixed_small_spp2.npz"))
     host = rt.HostScene(rt.scenes.mixed_small(width=64, height=48), lib)

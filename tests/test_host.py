@@ -18,7 +18,7 @@ def test_cabi_exports_every_declared_symbol(rt, lib):
     assert declared == set(capi.PROTOTYPES), declared ^ set(capi.PROTOTYPES)
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.rt_abi_version() == 2
+    assert lib.rt_abi_version() == 3
 
 
 def test_struct_layouts_match_reference_headers(rt):
@@ -99,9 +99,13 @@ def _blob_sections(blob):
     ints = struct.unpack_from("<8i", blob, 16)
     ntex, = struct.unpack_from("<Q", blob, 48)
     offs = struct.unpack_from("<7Q", blob, 56)
+    off_maxx, = struct.unpack_from("<Q", blob, 128)
+    off_tri_id, off_tri_pos = struct.unpack_from("<2Q", blob, 144)
+    q_base, num_nodes_q, topology = struct.unpack_from("<3i", blob, 160)
     return dict(magic=magic, version=ver, total=total, num_nodes=ints[0], num_tris=ints[1], num_meshes=ints[2],
                 num_objects=ints[3], root_is_leaf=ints[4], max_depth=ints[5], max_leaf=ints[6], num_nodes_ref=ints[7],
-                num_texels=ntex, offs=offs)
+                num_texels=ntex, offs=offs, off_maxx=off_maxx, off_tri_id=off_tri_id, off_tri_pos=off_tri_pos,
+                q_base=q_base, num_nodes_q=num_nodes_q, topology=topology)
 
 
 def test_flatten_structure(rt, lib, sim):
@@ -109,12 +113,16 @@ def test_flatten_structure(rt, lib, sim):
     outward-rounded supersets of the FP64 boxes."""
     desc = rt.scenes.office(width=16, height=9)
     host = rt.HostScene(desc, lib)
-    blob = sim.flatten(host)
+    blob = sim.flatten(host, rt.capi.RT_SCENE_REFERENCE_TOPOLOGY)
     h = _blob_sections(blob)
     n = host.nodes_used
     cnt = host.bvh_arrays["count"][:n]
     assert h["total"] == len(blob) and h["num_tris"] == 34000 and h["num_nodes_ref"] == n
     assert h["num_nodes"] == int((cnt == 0).sum()) and h["max_leaf"] == int(cnt.max())
+    assert h["topology"] == 1 and h["q_base"] == 0 and h["num_nodes_q"] == h["num_nodes"]
+    ident = np.arange(34000, dtype=np.int32)
+    assert np.array_equal(np.frombuffer(blob, np.int32, 34000, h["off_tri_id"]), ident)
+    assert np.array_equal(np.frombuffer(blob, np.int32, 34000, h["off_tri_pos"]), ident)
     nodes = np.frombuffer(blob, np.float32, h["num_nodes"] * 16, h["offs"][0]).reshape(-1, 16)
     refs = nodes[:, 12:16].view(np.int32)
     leaves = set()
@@ -143,6 +151,64 @@ def test_flatten_structure(rt, lib, sim):
             assert (c - hh <= mn[lc + s_, :3]).all() and (c + hh >= mx[lc + s_, :3]).all()
             if refs[flat][2 + s_] == 0:
                 todo.append((lc + s_, int(refs[flat][s_])))
+
+
+def test_flatten_builds_its_own_traversal_tree(rt, lib, sim):
+    """Default flatten: SAH tree in records [0, q_base), the reference tree unchanged behind it; every triangle
+    in exactly one SAH leaf, every child box contains the FP64 triangles below it, tri_id / tri_pos are inverse
+    permutations and the filter / exact records follow the SAH leaf order."""
+    desc = rt.scenes.office(width=16, height=9)
+    host = rt.HostScene(desc, lib)
+    ref = sim.flatten(host, rt.capi.RT_SCENE_REFERENCE_TOPOLOGY)
+    blob = sim.flatten(host)
+    hr, h = _blob_sections(ref), _blob_sections(blob)
+    N = 34000
+    assert h["topology"] == 0 and h["q_base"] > 0 and h["num_nodes_q"] == hr["num_nodes"]
+    assert h["num_nodes"] == h["q_base"] + h["num_nodes_q"]
+    nodes = np.frombuffer(blob, np.float32, h["num_nodes"] * 16, h["offs"][0]).reshape(-1, 16)
+    refs = nodes[:, 12:16].view(np.int32)
+    # the reference tree: same records, interior child references moved by q_base
+    rn = np.frombuffer(ref, np.float32, hr["num_nodes"] * 16, hr["offs"][0]).reshape(-1, 16)
+    rr = rn[:, 12:16].view(np.int32).copy()
+    rr[:, 0] += np.where(rr[:, 2] == 0, h["q_base"], 0)
+    rr[:, 1] += np.where(rr[:, 3] == 0, h["q_base"], 0)
+    assert np.array_equal(nodes[h["q_base"]:, :12], rn[:, :12]) and np.array_equal(refs[h["q_base"]:], rr)
+    assert blob[h["off_maxx"]:h["off_maxx"] + 16 * h["num_nodes_q"]] == ref[hr["off_maxx"]:hr["off_maxx"] + 16 * hr["num_nodes"]]
+    tri_id = np.frombuffer(blob, np.int32, N, h["off_tri_id"])
+    tri_pos = np.frombuffer(blob, np.int32, N, h["off_tri_pos"])
+    assert np.array_equal(np.sort(tri_id), np.arange(N)) and np.array_equal(tri_pos[tri_id], np.arange(N))
+    exact_r = np.frombuffer(ref, np.float64, N * 10, hr["offs"][2]).reshape(N, 10)
+    exact_s = np.frombuffer(blob, np.float64, N * 10, h["offs"][2]).reshape(N, 10)
+    assert np.array_equal(exact_s, exact_r[tri_id])
+    filt_r = np.frombuffer(ref, np.float32, N * 12, hr["offs"][1]).reshape(N, 12)
+    filt_s = np.frombuffer(blob, np.float32, N * 12, h["offs"][1]).reshape(N, 12)
+    assert np.array_equal(filt_s, filt_r[tri_id])
+    assert blob[h["offs"][3]:h["offs"][4]] == ref[hr["offs"][3]:hr["offs"][4]]      # TriShade stays in reference order
+    verts = exact_s[:, :9].reshape(N, 3, 3)
+    tmin, tmax = verts.min(1), verts.max(1)
+    covered = np.zeros(N, np.int32)
+
+    def walk(rec):
+        """returns the contiguous position range below record `rec`; checks both child boxes"""
+        lo_all, hi_all = N, 0
+        r = nodes[rec].astype(np.float64)
+        for s_, k in ((0, 0), (1, 6)):
+            c, hh = r[k:k + 3], r[k + 3:k + 6]
+            if refs[rec][2 + s_] > 0:
+                a, b = int(refs[rec][s_]), int(refs[rec][s_] + refs[rec][2 + s_])
+                covered[a:b] += 1
+            else:
+                a, b = walk(int(refs[rec][s_]))
+            assert (c - hh <= tmin[a:b].min(0)).all() and (c + hh >= tmax[a:b].max(0)).all()
+            lo_all, hi_all = min(lo_all, a), max(hi_all, b)
+        if refs[rec][2] > 0 and refs[rec][3] > 0:
+            assert refs[rec][1] == refs[rec][0] + refs[rec][2]      # sibling leaves own adjacent ranges
+        return lo_all, hi_all
+
+    import sys
+    sys.setrecursionlimit(10000)
+    assert walk(0) == (0, N) and (covered == 1).all()
+    assert h["max_depth"] <= 64
 
 
 def test_flatten_rejects_bad_input(rt, lib, sim):
