@@ -218,7 +218,7 @@ def run_b200(args):
     info = scene.info()
     cam = host.camera
     chunk = int(os.environ.get("RT_TILE_CHUNK", "0")) or None
-    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "3"))
+    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "4"))
     dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", "0.15"))
     FLUSH = int(os.environ.get("RT_FLUSH_MB", "160")) * 1024 * 1024             # > 126 MB L2 (env: experiments only)
     pipe = rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, tile_chunk=chunk,
