@@ -40,10 +40,10 @@ struct Ctx {
 // ---- cold per-lane state: shared memory columns on the device, a plain array on the host ----------
 enum ColdD { // double slots
   CD_O = 0, CD_D = 3, CD_BEST_T = 6, CD_P = 7, CD_N = 10, CD_V = 13, CD_KD = 16, CD_L = 19, CD_COL = 22,
-  CD_ACC = 25, CD_WEIGHT = 28, CD_NUM = 29
+  CD_ACC = 25, CD_WEIGHT = 28, CD_LDIR = 29 /* unit vector to the light under test */, CD_NUM = 32
 };
 enum ColdI { CI_PX = 0, CI_PY, CI_SAMPLE, CI_DEPTH, CI_MAT, CI_LIGHT, CI_NUM };
-constexpr int kColdBytesPerLane = CD_NUM * 8 + CI_NUM * 4; // 256
+constexpr int kColdBytesPerLane = CD_NUM * 8 + CI_NUM * 4; // 280
 
 template <int STRIDE> struct Cold {
   double *db; // &doubles[lane]
@@ -79,6 +79,12 @@ struct Mat {
 
 #ifndef RT_LDG
 #define RT_LDG 1
+#endif
+#ifndef RT_SKIP_BARY
+#define RT_SKIP_BARY 1
+#endif
+#ifndef RT_CACHE_LDIR
+#define RT_CACHE_LDIR 1
 #endif
 struct F4 {
   float x, y, z, w;
@@ -401,9 +407,12 @@ template <bool COUNT, int S> RT_HD void hit_setup(const Ctx &c, Hot &H, const Co
     const TriExact &e = sv.exact[sv.tri_pos[i]];
     TriHit h;
     h.t = best; h.alpha = 0.0; h.beta = 0.0; h.gamma = 0.0;
-    tri_exact(o, d, ld3(e.p0), ld3(e.p1), ld3(e.p2), h); // same arithmetic as the accepted test
     const TriShade &s = sv.shade[i];
     const MeshRec &mr = sv.meshes[s.mesh];
+    // barycentrics are needed for interpolated normals and texture coordinates only; the accepted test's t
+    // is CD_BEST_T bit for bit (same arithmetic), so flat untextured meshes skip the FP64 recomputation
+    if (!RT_SKIP_BARY || mr.draw_mode != 0 || mr.tex_w != -1)
+      tri_exact(o, d, ld3(e.p0), ld3(e.p1), ld3(e.p2), h); // same arithmetic as the accepted test
     mat = s.mesh;
     P = along(o, h.t, d);                                   // ray(t), mymesh.cpp:219
     kd = ld3(mr.diffuse);
@@ -445,11 +454,17 @@ template <bool COUNT, int S> RT_HD void hit_setup(const Ctx &c, Hot &H, const Co
 }
 
 // diffuse + specular of one unshadowed light, mytracer.cpp:510-534,581-585,603-605
-template <int S> RT_HD void add_light(const Ctx &c, const Cold<S> &C, const Mat &m, int k) {
+// cached: CD_LDIR holds normalize(light - P) of light k (set when its shadow ray was cast)
+template <int S> RT_HD void add_light(const Ctx &c, const Cold<S> &C, const Mat &m, int k, bool cached) {
   const double *lcol = c.light_col + 4 * k;
-  const D3 P = C.v(CD_P), N = C.v(CD_N);
-  const D3 lv = sub(ld3(c.light_pos + 4 * k), P);
-  const D3 l = normalize(lv);
+  const D3 N = C.v(CD_N);
+  D3 l;
+  if (RT_CACHE_LDIR && cached) {
+    l = C.v(CD_LDIR);
+  } else {
+    const D3 lv = sub(ld3(c.light_pos + 4 * k), C.v(CD_P));
+    l = normalize(lv);
+  }
   const double diff = dmax0(dot(N, l));
   double refl = 0.0;
   if (diff > 0.0) {
@@ -485,7 +500,7 @@ template <bool COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold
       hit_setup<COUNT>(c, H, C, m);
     } else { // M_ANYHIT finished: CI_LIGHT was the light under test
       load_mat(sv, C.i(CI_MAT), m);
-      if (!H.found) add_light(c, C, m, C.i(CI_LIGHT));
+      if (!H.found) add_light(c, C, m, C.i(CI_LIGHT), true);
       C.i(CI_LIGHT) = C.i(CI_LIGHT) + 1;
     }
     H.mode = M_SHADE;
@@ -507,10 +522,11 @@ template <bool COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold
           ++k;
           continue;
         }
+        if (RT_CACHE_LDIR) C.set(CD_LDIR, ldir);
         start_ray<COUNT>(c, H, C, add(P, scale(1e-4, ldir)), ldir, M_ANYHIT, ldist);
         break;
       }
-      add_light(c, C, m, k);
+      add_light(c, C, m, k, false);
       ++k;
     }
     C.i(CI_LIGHT) = k;

@@ -3,9 +3,10 @@
 // Replaces compute_image_device (mytracer_gpu.cu:119-160: one thread per pixel, 16x16 blocks,
 // FP64 recursion-free but stack-in-local-memory traversal).  Here:
 //   * the grid is sized to the machine (SM count x resident CTAs), not to the image;
-//   * each warp keeps all 32 lanes busy: whenever lanes go idle, lane 0 claims that many work
+//   * warp-level work fetch: when the lanes of a warp are idle, one lane claims that many work
 //     slots with ONE atomicAdd and the slots are handed out by __ballot/__popc rank
-//     (north star (b): "warp-level work fetch (atomics plus __shfl / __ballot)");
+//     (north star (b): "warp-level work fetch (atomics plus __shfl / __ballot)"); by default a warp
+//     refills when all 32 lanes are idle, i.e. it takes one 8x4 tile at a time;
 //   * work slots follow 8x4-pixel tiles so that a freshly filled warp covers a compact screen
 //     patch (coherent primary rays);
 //   * every lane runs the rt_core.cuh state machine; the traversal loop is shared by primary,
@@ -101,7 +102,15 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
 
     // ---- warp-level work fetch for idle lanes ----------------------------------------------
     const unsigned idle = __ballot_sync(kFullMask, H.mode == M_IDLE);
+    // A warp takes new pixels only when ALL its lanes are idle: the 32 pixels of a tile then move through the
+    // path stages together (primary rays, then the shadow rays of light 0, ...), which keeps both the traversal
+    // and the FP64 path logic coherent.  Refilling single lanes as they finish keeps more lanes busy but mixes
+    // ray generations in a warp and is 17 % slower (RT_REFILL_PARTIAL; profiles/r01_variants.md).
+#ifdef RT_REFILL_PARTIAL
     if (idle != 0u && !exhausted) {
+#else
+    if (idle == kFullMask && !exhausted) {
+#endif
       const int n = __popc(idle);
       const int leader = __ffs(idle) - 1;
       const int rank_in_idle = __popc(idle & ((1u << lane) - 1u));

@@ -16,11 +16,17 @@
 namespace rtb {
 namespace {
 
-constexpr int kLeafMax = 4;
+#ifndef RT_SAH_LEAFMAX
+#define RT_SAH_LEAFMAX 4
+#endif
+#ifndef RT_SAH_TRAV
+#define RT_SAH_TRAV 1.2f
+#endif
+constexpr int kLeafMax = RT_SAH_LEAFMAX;
 constexpr int kBins = 32;
 constexpr int kSweepMax = 96;     // exact sweep at or below this many primitives
 constexpr int kDepthSwitch = 36;  // 36 SAH levels + log2(remaining) median levels < kStackMax (64)
-constexpr float kTrav = 1.2f;     // cost of one two-box traversal step relative to one triangle test
+constexpr float kTrav = RT_SAH_TRAV;    // cost of one two-box traversal step relative to one triangle test
 
 struct Box {
   float lo[3], hi[3];
