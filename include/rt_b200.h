@@ -256,9 +256,44 @@ int rt_bvh_build_median_device(rt_data_soa *data, rt_bvh_nodes_soa *nodes, int *
  * vertex normals.  pos/vnormals: nv vec4; idx: 3*nt local vertex ids; fnormals: nt vec4. */
 int rt_compute_normals(const rt_vec4 *pos, int nv, const int *idx, int nt, rt_vec4 *fnormals,
                        rt_vec4 *vnormals);
+/* The same on the GPU, bit-identical (per-vertex accumulation in the reference's triangle order: stable sort
+ * of the corners by vertex).  Host or managed pointers; device_ms (may be NULL) = kernel time. */
+int rt_compute_normals_device(const rt_vec4 *pos, int nv, const int *idx, int nt, rt_vec4 *fnormals,
+                              rt_vec4 *vnormals, double *device_ms);
 /* Pinhole camera from eye/center/up/fovy(deg) (build-defined; DESIGN.md "Conventions"). */
 int rt_camera_look_at(const double eye[3], const double center[3], const double up[3], double fovy_deg,
                       int width, int height, rt_camera *out);
+
+/* ---- caller side of the boundary: scene files and images ---------------------- */
+/* Scene ingestion == the course framework's read_scene/read_obj (absent; format: rt_scene_io.cpp) followed by
+ * Raytracer::build_Data (mytracer.cpp:166-296), Mesh::compute_normals and BVH::initSoA: a `.sce` file with
+ * OBJ meshes and PPM/PNG textures becomes exactly the arrays rt_scene_create takes.  Host-side; the flags
+ * move the normals and the BVH build to the GPU (same results). */
+#define RT_LOAD_DEVICE_BVH     1u
+#define RT_LOAD_DEVICE_NORMALS 2u
+typedef struct rt_scene_file rt_scene_file;
+typedef struct rt_scene_file_view {
+  rt_data_soa data;            /* pointers into the rt_scene_file; triangle rows already in BVH order */
+  rt_bvh_nodes_soa bvh;
+  int nodes_used;
+  const rt_object *objects;
+  int num_objects;
+  rt_camera camera;
+  const rt_vec4 *lights_pos, *lights_color;
+  int num_lights;
+  rt_vec4 background, ambience;
+  int max_depth;
+} rt_scene_file_view;
+int rt_scene_file_load(const char *path, unsigned load_flags, rt_scene_file **out);
+int rt_scene_file_get(const rt_scene_file *file, rt_scene_file_view *out);
+int rt_scene_file_free(rt_scene_file *file);
+/* Frame buffer (index y*W + x, y = 0 is the BOTTOM row: lower_left + y*y_dir) -> upright `.png` (8-bit RGBA)
+ * or, for any other extension, binary PPM.  The reference writes its frames through the absent Image class
+ * (outputs/ *.png). */
+int rt_image_write(const char *path, const uint8_t *rgba8, int width, int height);
+/* PPM (P6) or PNG (8-bit, non-interlaced) -> malloc'ed RGBA8, row 0 = top row; release with rt_image_free. */
+int rt_image_read(const char *path, int *width, int *height, uint8_t **rgba8);
+int rt_image_free(uint8_t *rgba8);
 
 #ifdef __cplusplus
 }

@@ -110,6 +110,14 @@ class SceneInfo(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class SceneFileView(C.Structure):
+    _fields_ = [("data", DataSoA), ("bvh", BvhNodesSoA), ("nodes_used", C.c_int), ("objects", C.POINTER(Object)),
+                ("num_objects", C.c_int), ("camera", Camera), ("lights_pos", Vec4_p), ("lights_color", Vec4_p),
+                ("num_lights", C.c_int), ("background", Vec4), ("ambience", Vec4), ("max_depth", C.c_int)]
+
+
+RT_LOAD_DEVICE_BVH, RT_LOAD_DEVICE_NORMALS = 1, 2
+
 # every symbol include/rt_b200.h declares: name -> (restype, argtypes)
 PROTOTYPES = {
     "rt_init_device": (C.c_int, [C.c_int]),
@@ -142,6 +150,13 @@ PROTOTYPES = {
     "rt_bvh_build_median": (C.c_int, [C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), c_int_p]),
     "rt_bvh_build_median_device": (C.c_int, [C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), c_int_p, c_double_p]),
     "rt_compute_normals": (C.c_int, [Vec4_p, C.c_int, c_int_p, C.c_int, Vec4_p, Vec4_p]),
+    "rt_compute_normals_device": (C.c_int, [Vec4_p, C.c_int, c_int_p, C.c_int, Vec4_p, Vec4_p, c_double_p]),
+    "rt_scene_file_load": (C.c_int, [C.c_char_p, C.c_uint, C.POINTER(C.c_void_p)]),
+    "rt_scene_file_get": (C.c_int, [C.c_void_p, C.POINTER(SceneFileView)]),
+    "rt_scene_file_free": (C.c_int, [C.c_void_p]),
+    "rt_image_write": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int, C.c_int]),
+    "rt_image_read": (C.c_int, [C.c_char_p, c_int_p, c_int_p, C.POINTER(C.c_void_p)]),
+    "rt_image_free": (C.c_int, [C.c_void_p]),
     "rt_camera_look_at": (C.c_int, [c_double_p, c_double_p, c_double_p, C.c_double, C.c_int, C.c_int,
                                     C.POINTER(Camera)]),
 }

@@ -91,8 +91,9 @@ def look_at(cam: dict, lib=None) -> Camera:
 class HostScene:
     """Data SoA (mydata.h) + BVHNodes_SoA (mybvh.h) as numpy arrays, built like the reference does."""
 
-    def __init__(self, desc: SceneDesc, lib=None, gpu_build=False):
-        """gpu_build: BVH through rt_bvh_build_median_device (same result, built on the GPU)."""
+    def __init__(self, desc: SceneDesc, lib=None, gpu_build=False, gpu_normals=False):
+        """gpu_build: BVH through rt_bvh_build_median_device; gpu_normals: normals through
+        rt_compute_normals_device (same results, computed on the GPU)."""
         self.lib = lib or capi.load_library()
         self.desc = desc
         lib = self.lib
@@ -127,7 +128,11 @@ class HostScene:
             pos4 = _vec4_array(m.pos)
             fn = np.zeros((n_t, 4)); vn = np.zeros((n_v, 4))
             idx = np.ascontiguousarray(m.idx.reshape(-1))
-            check(lib.rt_compute_normals(_p(pos4, Vec4_p), n_v, _p(idx, c_int_p), n_t, _p(fn, Vec4_p), _p(vn, Vec4_p)), lib)
+            if gpu_normals:
+                check(lib.rt_compute_normals_device(_p(pos4, Vec4_p), n_v, _p(idx, c_int_p), n_t, _p(fn, Vec4_p),
+                                                    _p(vn, Vec4_p), None), lib)
+            else:
+                check(lib.rt_compute_normals(_p(pos4, Vec4_p), n_v, _p(idx, c_int_p), n_t, _p(fn, Vec4_p), _p(vn, Vec4_p)), lib)
             # per-vertex block (mytracer.cpp:222-232)
             a["vertexPos"][vbase:vbase + n_v] = pos4
             a["vertexNormals"][vbase:vbase + n_v] = vn

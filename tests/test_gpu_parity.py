@@ -206,6 +206,26 @@ def test_gpu_bvh_build_is_bit_identical_to_the_host_build(rt, lib, gpu):
             assert np.array_equal(a.arrays[k], b.arrays[k], equal_nan=(k == "normals")), (d.name, k)   # degenerate faces: NaN normals
 
 
+@pytest.mark.parametrize("name,kw", [("rings", dict(width=32, height=32, nu=96, nv=24)),
+                                     ("textured", dict(width=32, height=32, tex_size=16, slices=64, stacks=32)),
+                                     ("mixed_small", dict(width=32, height=32)),
+                                     ("office", dict(width=32, height=32))])
+def test_gpu_normals_are_bit_identical_to_the_host(rt, lib, gpu, name, kw):
+    """rt_compute_normals_device == rt_compute_normals (== Mesh::compute_normals, mymesh.cpp:103-163): face and
+    angle-weighted vertex normals, every mesh of the scene, bit for bit (degenerate faces give NaN on both)."""
+    desc = rt.scenes.REGISTRY[name](**kw)
+    a = rt.HostScene(desc, lib)
+    b = rt.HostScene(desc, lib, gpu_normals=True)
+    assert np.array_equal(a.arrays["normals"], b.arrays["normals"], equal_nan=True)
+    assert np.array_equal(a.arrays["vertexNormals"], b.arrays["vertexNormals"], equal_nan=True)
+    assert np.isfinite(b.arrays["vertexNormals"]).mean() > 0.99
+    # error behaviour: an out-of-range vertex index is reported, not dereferenced
+    pos = np.zeros((3, 4)); idx = np.array([0, 1, 7], np.int32); fn = np.zeros((1, 4)); vn = np.zeros((3, 4))
+    st = lib.rt_compute_normals_device(pos.ctypes.data_as(gpu.Vec4_p), 3, idx.ctypes.data_as(gpu.c_int_p), 1,
+                                       fn.ctypes.data_as(gpu.Vec4_p), vn.ctypes.data_as(gpu.Vec4_p), None)
+    assert st == gpu.RT_ERR_BAD_SCENE
+
+
 def test_full_size_properties(rt, lib, gpu, orc, oracle_kind):
     """BASELINE config 2 at full size (Office 34 k triangles, 1920x1080): determinism across launches,
     filter == exact-only, a checksum of the tile-sharded union, and oracle parity on a row sample."""
@@ -260,3 +280,21 @@ def test_drop_in_launch_with_adaptive_supersampling(rt, lib, gpu, orc, oracle_ki
     assert np.abs(h_img[..., :3] - expect).max() < 1e-6
     assert np.array_equal(d_tmp.cpu().numpy().reshape(H, W, 4)[..., :3][~flagged], h_img[..., :3][~flagged])
     lib.rt_scene_destroy(cache)
+
+
+def test_scene_file_to_image_on_the_gpu(rt, lib, gpu, tmp_path):
+    """The whole caller-side chain through the C ABI: .sce/.obj/.png files -> rt_scene_file_load with the normals
+    and the BVH built on the GPU -> rt_scene_create -> rt_render -> rt_image_write; equal to the in-memory scene
+    built on the host, and the PNG on disk is the upright frame."""
+    desc = rt.scenes.textured(width=192, height=108, tex_size=64, slices=32, stacks=16)
+    rt.scene_files.quantize_textures(desc)
+    path = rt.write_scene(desc, str(tmp_path))
+    fs = rt.FileScene(path, lib, gpu.RT_LOAD_DEVICE_BVH | gpu.RT_LOAD_DEVICE_NORMALS)
+    host = rt.HostScene(desc, lib)
+    a = rt.DeviceScene(host).render(host.camera, host.lights_pos, host.lights_color, host.params())
+    b = rt.DeviceScene(fs).render(fs.camera, fs.lights_pos, fs.lights_color, fs.params())
+    for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+        assert np.array_equal(a[k], b[k]), k
+    out = str(tmp_path / "frame.png")
+    rt.write_image(out, b["rgba8"], lib)
+    assert np.array_equal(rt.read_image(out, lib), b["rgba8"][::-1])
