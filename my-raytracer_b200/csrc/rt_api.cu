@@ -102,6 +102,7 @@ int adopt_blob(rt_scene *s) {
   s->view.shade = reinterpret_cast<const TriShade *>(b + h.off_shade);
   s->view.meshes = reinterpret_cast<const MeshRec *>(b + h.off_meshes);
   s->view.objects = reinterpret_cast<const ObjectRec *>(b + h.off_objects);
+  s->view.objfilt = reinterpret_cast<const ObjFilter *>(b + h.off_objfilt);
   s->view.texels = reinterpret_cast<const float *>(b + h.off_texels);
   s->view.num_nodes = h.num_nodes; s->view.num_tris = h.num_tris;
   s->view.num_meshes = h.num_meshes; s->view.num_objects = h.num_objects;
@@ -154,6 +155,10 @@ int adopt_blob(rt_scene *s) {
   if (s->extra_smem) {
     RT_CUDA(cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
     RT_CUDA(cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+  }
+  if (const char *e = std::getenv("RT_CARVEOUT")) { // experiments only: shared-memory carveout in percent
+    RT_CUDA(cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e)));
+    RT_CUDA(cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e)));
   }
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, render_kernel<false>, kBlockThreads, s->extra_smem));
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, render_kernel<true>, kBlockThreads, s->extra_smem));

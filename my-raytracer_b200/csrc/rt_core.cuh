@@ -20,6 +20,13 @@
 #define RTB_CORE_CUH
 #include "rt_intersect.cuh"
 
+#ifndef RT_SKIP_BARY
+#define RT_SKIP_BARY 1
+#endif
+#ifndef RT_CACHE_LDIR
+#define RT_CACHE_LDIR 1
+#endif
+
 namespace rtb {
 
 enum Mode : int { M_IDLE = 0, M_NEAREST = 1, M_ANYHIT = 2, M_SHADE = 3 };
@@ -40,7 +47,8 @@ struct Ctx {
 // ---- cold per-lane state: shared memory columns on the device, a plain array on the host ----------
 enum ColdD { // double slots
   CD_O = 0, CD_D = 3, CD_BEST_T = 6, CD_P = 7, CD_N = 10, CD_V = 13, CD_KD = 16, CD_L = 19, CD_COL = 22,
-  CD_ACC = 25, CD_WEIGHT = 28, CD_LDIR = 29 /* unit vector to the light under test */, CD_NUM = 32
+  CD_ACC = 25, CD_WEIGHT = 28, CD_LDIR = 29 /* unit vector to the light under test */,
+  CD_NUM = RT_CACHE_LDIR ? 32 : 29
 };
 enum ColdI { CI_PX = 0, CI_PY, CI_SAMPLE, CI_DEPTH, CI_MAT, CI_LIGHT, CI_NUM };
 constexpr int kColdBytesPerLane = CD_NUM * 8 + CI_NUM * 4; // 280
@@ -80,12 +88,7 @@ struct Mat {
 #ifndef RT_LDG
 #define RT_LDG 1
 #endif
-#ifndef RT_SKIP_BARY
-#define RT_SKIP_BARY 1
-#endif
-#ifndef RT_CACHE_LDIR
-#define RT_CACHE_LDIR 1
-#endif
+
 struct F4 {
   float x, y, z, w;
 };
@@ -192,12 +195,16 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   const bool exact_only = (c.fp.flags & 1) != 0;
   const SceneView &sv = c.sv;
   for (int k = 0; k < sv.num_objects; ++k) {
-    const ObjectRec &ob = sv.objects[k];
     double t;
     bump<COUNT>(c, C_OBJECT);
-    // FP32 pre-filter (a 4-wide batched variant of this loop was measured and is slower: 4.6 vs 3.2 ms on the
-    // molecule scene, the loop is latency-bound at 250 k pixels, not throughput-bound)
-    if (ob.kind == 0 && !exact_only && !sphere_filter(H.rf, ob.cf, ob.rf, ob.cabs, othi)) continue;
+    // FP32 pre-filter on the 32-byte ObjFilter record (a 4-wide batched variant of this loop was measured and is
+    // slower: 4.6 vs 3.2 ms on the molecule scene, the loop is latency-bound at 250 k pixels)
+    const char *fp = reinterpret_cast<const char *>(sv.objfilt + k);
+    const F4 f0 = ld_f4(fp);
+    const I4 f1 = ld_i4(fp + 16);
+    const float fc[3] = {f0.x, f0.y, f0.z};
+    if (f1.y == 0 && !exact_only && !sphere_filter(H.rf, fc, f0.w, __int_as_float_rt(f1.x), othi)) continue;
+    const ObjectRec &ob = sv.objects[k];
     const bool hit = (ob.kind == 0) ? sphere_exact(o, d, ld3(ob.center), ob.radius, t)
                                     : plane_exact(o, d, ld3(ob.center), ld3(ob.normal), t);
     if (hit && t < best) {

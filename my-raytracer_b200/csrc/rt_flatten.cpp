@@ -351,6 +351,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     }
   }
   std::vector<ObjectRec> objs(num_objects);
+  std::vector<ObjFilter> objf(num_objects);
   for (int k = 0; k < num_objects; ++k) {
     const rt_object &o = objects[k];
     if (o.kind != RT_SPHERE && o.kind != RT_PLANE) { err = "flatten: unknown object kind"; return RT_ERR_INVALID_ARG; }
@@ -369,6 +370,10 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     for (int a = 0; a < 3; ++a) r.cf[a] = (float)r.center[a];
     r.rf = (float)o.radius;
     r.cabs = round_up(std::fabs(r.center[0]) + std::fabs(r.center[1]) + std::fabs(r.center[2]));
+    ObjFilter &q = objf[k];
+    std::memset(&q, 0, sizeof(q));
+    for (int a = 0; a < 3; ++a) q.c[a] = r.cf[a];
+    q.r = r.rf; q.cabs = r.cabs; q.kind = r.kind;
   }
 
   // ---- 4. assemble -----------------------------------------------------------------------------
@@ -391,6 +396,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.off_maxx = off;    off = align_up(off + maxx.size() * sizeof(NodeMaxX), kSectionAlign);
   h.off_tri_id = off;  off = align_up(off + tri_id.size() * sizeof(int32_t), kSectionAlign);
   h.off_tri_pos = off; off = align_up(off + tri_pos.size() * sizeof(int32_t), kSectionAlign);
+  h.off_objfilt = off; off = align_up(off + objf.size() * sizeof(ObjFilter), kSectionAlign);
   h.q_base = q_base; h.num_nodes_q = num_nodes_q; h.topology = topology;
   h.root_max_x = N > 0 ? bvh->bb_max_[0].x : 0.0;
   h.total_bytes = off;
@@ -407,6 +413,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   }
   if (num_meshes > 0) std::memcpy(blob.data() + h.off_meshes, meshes.data(), meshes.size() * sizeof(MeshRec));
   if (num_objects > 0) std::memcpy(blob.data() + h.off_objects, objs.data(), objs.size() * sizeof(ObjectRec));
+  if (num_objects > 0) std::memcpy(blob.data() + h.off_objfilt, objf.data(), objf.size() * sizeof(ObjFilter));
   float *tx = reinterpret_cast<float *>(blob.data() + h.off_texels);
   for (size_t t = 0; t < num_texels; ++t) {
     const rt_vec4 &c = data->meshTexels_[t];
@@ -430,7 +437,8 @@ int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
                   h.off_texels + h.num_texels * 16 <= h.off_maxx &&
                   h.off_maxx + (size_t)h.num_nodes_q * sizeof(NodeMaxX) <= h.off_tri_id &&
                   h.off_tri_id + (size_t)h.num_tris * sizeof(int32_t) <= h.off_tri_pos &&
-                  h.off_tri_pos + (size_t)h.num_tris * sizeof(int32_t) <= h.total_bytes &&
+                  h.off_tri_pos + (size_t)h.num_tris * sizeof(int32_t) <= h.off_objfilt &&
+                  h.off_objfilt + (size_t)h.num_objects * sizeof(ObjFilter) <= h.total_bytes &&
                   h.q_base >= 0 && h.num_nodes_q >= 0 && (size_t)h.q_base + (size_t)h.num_nodes_q == (size_t)h.num_nodes;
   if (!ok) { err = "blob: section table inconsistent"; return RT_ERR_BAD_SCENE; }
   return RT_OK;
@@ -446,6 +454,7 @@ SceneView view_of_blob(const unsigned char *blob) {
   v.shade = reinterpret_cast<const TriShade *>(blob + h.off_shade);
   v.meshes = reinterpret_cast<const MeshRec *>(blob + h.off_meshes);
   v.objects = reinterpret_cast<const ObjectRec *>(blob + h.off_objects);
+  v.objfilt = reinterpret_cast<const ObjFilter *>(blob + h.off_objfilt);
   v.texels = reinterpret_cast<const float *>(blob + h.off_texels);
   v.tex_objs = nullptr;
   v.maxx = reinterpret_cast<const NodeMaxX *>(blob + h.off_maxx);

@@ -20,6 +20,7 @@ namespace rtb {
 
 constexpr int kBlockThreads = 128;
 constexpr unsigned kFullMask = 0xffffffffu;
+constexpr int kPartialRefillObjects = 32; // at or above this many analytic primitives lanes are refilled one by one
 
 struct KernelArgs {
   SceneView sv;
@@ -92,6 +93,7 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
   const long long slots = work_slots(c);
   const long long nchunks = a.dyn_counter ? pool_chunks(c) : 0;
   const unsigned lane = threadIdx.x & 31u;
+  const bool partial_refill = c.sv.num_objects >= kPartialRefillObjects;
   bool exhausted = false;   // warp-uniform: no work left anywhere
   bool local_done = false;  // warp-uniform: this rank's static share is drained
   long long wp_next = 0, wp_end = 0; // warp-private range of dynamic-pool slots (warp-uniform)
@@ -106,10 +108,13 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     // path stages together (primary rays, then the shadow rays of light 0, ...), which keeps both the traversal
     // and the FP64 path logic coherent.  Refilling single lanes as they finish keeps more lanes busy but mixes
     // ray generations in a warp and is 17 % slower (RT_REFILL_PARTIAL; profiles/r01_variants.md).
+    // Exception: scenes dominated by the linear list of analytic primitives (the reference has no BVH over
+    // objects_): every ray walks the same list in lockstep whatever its generation, so there is no coherence
+    // to protect and full lanes win (molecule, 602 objects: 2.9 ms against 4.1 ms).
 #ifdef RT_REFILL_PARTIAL
     if (idle != 0u && !exhausted) {
 #else
-    if (idle == kFullMask && !exhausted) {
+    if ((partial_refill ? idle != 0u : idle == kFullMask) && !exhausted) {
 #endif
       const int n = __popc(idle);
       const int leader = __ffs(idle) - 1;

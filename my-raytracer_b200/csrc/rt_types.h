@@ -4,7 +4,7 @@
 // One contiguous, 512-byte-sectioned blob (so it can be broadcast with a single NCCL call):
 //
 //   BlobHeader | NodeRec[] | TriFilter[] | TriExact[] | TriShade[] | MeshRec[] | ObjectRec[] | texels | NodeMaxX[]
-//              | tri_id[] | tri_pos[]
+//              | tri_id[] | tri_pos[] | ObjFilter[]
 //
 // Two trees share the NodeRec array (rt_sah.h): records [0, q_base) are the product's SAH traversal tree,
 // records [q_base, q_base + num_nodes_q) the reference's median-split tree, walked only by rays with
@@ -40,7 +40,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 6;
+constexpr uint32_t kBlobVersion = 7;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -102,6 +102,17 @@ struct alignas(16) ObjectRec {
 };
 static_assert(sizeof(ObjectRec) == 176, "ObjectRec must be 176 bytes");
 
+// 32 B per analytic primitive: everything the per-ray loop over Raytracer::objects_ touches before a sphere
+// survives its FP32 pre-filter.  602 spheres = 19 KB, L1-resident next to the cold state (the 176-byte
+// ObjectRec list is 106 KB and falls out of a 92 KB L1: 4.1 instead of 3.1 ms on the molecule scene).
+struct alignas(16) ObjFilter {
+  float c[3], r;   // centre and radius rounded to FP32
+  float cabs;      // |cx| + |cy| + |cz| (error bound)
+  int32_t kind;    // 0 sphere, 1 plane (planes have no filter)
+  int32_t pad[2];
+};
+static_assert(sizeof(ObjFilter) == 32, "ObjFilter must be 32 bytes");
+
 struct alignas(16) NodeMaxX {
   double c0_max_x, c1_max_x;
 };
@@ -124,7 +135,8 @@ struct BlobHeader {
   int32_t num_nodes_q; // its record count; num_nodes = total records of both trees
   int32_t topology;    // 0 SAH traversal tree + reference tree, 1 reference tree only
   int32_t pad_i;
-  uint64_t reserved[2];
+  uint64_t off_objfilt; // ObjFilter[num_objects]
+  uint64_t reserved[1];
 };
 static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
 
@@ -136,6 +148,7 @@ struct SceneView {
   const TriShade *shade;
   const MeshRec *meshes;
   const ObjectRec *objects;
+  const ObjFilter *objfilt;
   const float *texels; // 4 floats per texel (host/test build); the kernel uses tex_objs instead
   const unsigned long long *tex_objs; // cudaTextureObject_t per mesh (0 when untextured)
   const NodeMaxX *maxx;

@@ -1,4 +1,4 @@
-"""Times kernel variants (my-raytracer_b200/variants/*.so) on Office 1080p and checks each against the
+"""Times kernel variants (my-raytracer_b200/variants/*.so) on Office 1080p (or RT_SCENE=<name>) and checks each against the
 first one bit for bit.  Usage: python tools/gpu_variants.py [names...]"""
 import os, subprocess, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -11,7 +11,7 @@ rt = rtpkg.load()
 from my_raytracer_b200 import capi
 lib = rt.load_library()
 capi.check(lib.rt_init_device(0), lib)
-desc = rt.scenes.office()
+desc = rt.scenes.REGISTRY[os.environ.get("RT_SCENE", "office")]()
 host = rt.HostScene(desc, lib)
 dev = rt.DeviceScene(host)
 ms = []
