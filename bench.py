@@ -218,11 +218,15 @@ def run_b200(args):
     info = scene.info()
     cam = host.camera
     chunk = int(os.environ.get("RT_TILE_CHUNK", "0")) or None
-    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "4"))
+    # frames in flight: 4 full-width grids up to 4 GPUs; at 8 GPUs a frame is ~0.25 ms, comparable to the time of a
+    # single heavy tile, so 8 frames are kept in flight on quarter-width grids (1 CTA per SM each: four frames are
+    # resident side by side and every warp renders 4x more tiles of its frame) - profiles/r01_variants.md
+    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "8" if world >= 8 else "4"))
     dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", "0.15"))
     FLUSH = int(os.environ.get("RT_FLUSH_MB", "160")) * 1024 * 1024             # > 126 MB L2 (env: experiments only)
+    ctas = int(os.environ.get("RT_CTAS_PER_SM", "1" if world >= 8 else "0"))     # 0 = full-width grids
     pipe = rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, tile_chunk=chunk,
-                               dyn_fraction=dyn_fraction, flush_bytes=FLUSH)
+                               dyn_fraction=dyn_fraction, flush_bytes=FLUSH, ctas_per_sm=ctas)
     nl = pipe.nl
     stream = torch.cuda.current_stream()
 
@@ -279,6 +283,7 @@ def run_b200(args):
 
     # ---- one frame at a time (latency): serial launches, CUDA events around the kernel ---------------------
     sparams = host.params(tile=pipe.tile, flags=capi.RT_FLAG_NO_CLEAR)
+    capi.check(lib.rt_scene_set_launch_width(scene.handle, 0), lib)     # one frame alone gets the whole machine
     kern_ms = []
     for i in range(8):
         pipe.flush.fill_(1)
@@ -362,7 +367,7 @@ def run_b200(args):
                        "traversal_records": info["num_nodes_traversal"],
                        "lights": nl, "max_depth": desc.max_depth, "spp": 1,
                        "l2": "flushed before every timed frame (160 MiB fill on the frame's stream)",
-                       "frames_in_flight": pipe.depth,
+                       "frames_in_flight": pipe.depth, "ctas_per_sm_per_frame": pipe.ctas_per_sm or "all",
                        "parallelism": f"tiles{world}" if world > 1 else "single",
                        "tile_chunk": pipe.tile[2], "dyn_tiles": pipe.dyn_tiles, "dyn_chunk": pipe.dyn_chunk,
                        "gather": "fused: peer stores into rank 0's frame buffer over NVLink + 4-byte all-reduce signal"

@@ -192,6 +192,11 @@ int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const 
 int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
                        int num_objects, unsigned scene_flags, rt_scene **out);
 int rt_scene_destroy(rt_scene *scene);
+/* Persistent-grid width of the following launches: ctas_per_sm resident CTAs per SM (0 = all the kernel's
+ * occupancy allows, the default).  A host that keeps D frames in flight on D streams sets occupancy / D so that
+ * the D grids run side by side (each warp then renders D times more tiles of its frame, which balances short
+ * multi-GPU frames) instead of queueing for each other's CTA slots. */
+int rt_scene_set_launch_width(rt_scene *scene, int ctas_per_sm);
 int rt_scene_get_info(const rt_scene *scene, rt_scene_info *out);
 
 /* Multi-GPU replication: rank 0 exports the flattened blob (host copy), the caller broadcasts

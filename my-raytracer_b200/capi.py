@@ -128,6 +128,7 @@ PROTOTYPES = {
     "rt_scene_create_ex": (C.c_int, [C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), C.POINTER(Object), C.c_int, C.c_uint,
                                      C.POINTER(C.c_void_p)]),
     "rt_scene_destroy": (C.c_int, [C.c_void_p]),
+    "rt_scene_set_launch_width": (C.c_int, [C.c_void_p, C.c_int]),
     "rt_scene_get_info": (C.c_int, [C.c_void_p, C.POINTER(SceneInfo)]),
     "rt_scene_blob_size": (C.c_int, [C.c_void_p, c_size_p]),
     "rt_scene_blob_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),

@@ -62,6 +62,7 @@ struct rt_scene {
   int *d_list = nullptr; // supersampling pixel list
   size_t cap_list = 0;
   int grid_plain = 0, grid_count = 0;
+  int sm_count = 0, ctas_per_sm = 0; // ctas_per_sm: 0 = every resident slot (rt_scene_set_launch_width)
   size_t extra_smem = 0;
   rt_counters counters;
   rt_scene_info info;
@@ -162,6 +163,7 @@ int adopt_blob(rt_scene *s) {
   }
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, render_kernel<false>, kBlockThreads, s->extra_smem));
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, render_kernel<true>, kBlockThreads, s->extra_smem));
+  s->sm_count = prop.multiProcessorCount;
   s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
   s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
   {
@@ -205,8 +207,16 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   }
 #endif
   RT_CUDA(cudaEventRecord(s->ev0[slot], st));
-  if (count) render_kernel<true><<<s->grid_count, kBlockThreads, s->extra_smem, st>>>(a);
-  else render_kernel<false><<<s->grid_plain, kBlockThreads, s->extra_smem, st>>>(a);
+  // frames in flight share the machine: with ctas_per_sm = k each launch takes k of the resident CTA slots of
+  // every SM, so several persistent grids run side by side instead of queueing for each other's slots
+  int gc = s->grid_count, gp = s->grid_plain;
+  if (s->ctas_per_sm > 0) {
+    const int lim = s->sm_count * s->ctas_per_sm;
+    gc = gc < lim ? gc : lim;
+    gp = gp < lim ? gp : lim;
+  }
+  if (count) render_kernel<true><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
+  else render_kernel<false><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
   RT_CUDA(cudaGetLastError());
   RT_CUDA(cudaEventRecord(s->ev1[slot], st));
   s->timed = true;
@@ -299,6 +309,12 @@ int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, con
   st = rt_scene_create_from_blob(blob.data(), blob.size(), 0, out);
   if (st == RT_OK) (*out)->info.flatten_ms = flat_ms;
   return st;
+}
+
+int rt_scene_set_launch_width(rt_scene *s, int ctas_per_sm) {
+  if (!s || ctas_per_sm < 0) { set_error("rt_scene_set_launch_width: invalid argument"); return RT_ERR_INVALID_ARG; }
+  s->ctas_per_sm = ctas_per_sm;
+  return RT_OK;
 }
 
 int rt_scene_destroy(rt_scene *s) {

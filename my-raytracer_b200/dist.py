@@ -103,7 +103,7 @@ class FramePipeline:
     """
 
     def __init__(self, lib, scene_handle, host_scene, device, width, height, depth=2, ring=4, tile_chunk=None,
-                 dyn_fraction=0.15, flush_bytes=0):
+                 dyn_fraction=0.15, flush_bytes=0, ctas_per_sm=0):
         import ctypes as C
         from . import capi
         self.C, self.capi, self.lib = C, capi, lib
@@ -158,6 +158,10 @@ class FramePipeline:
                                                  dyn=(self.dyn_tiles, self.dyn_chunk,
                                                       (self.ctr_ptr + 64 * s) if self.dyn_tiles else None)))
         self.submitted = 0
+        # ctas_per_sm > 0: every frame's persistent grid takes only that many CTA slots per SM, so the frames in
+        # flight run side by side (rt_scene_set_launch_width)
+        self.ctas_per_sm = int(ctas_per_sm)
+        capi.check(lib.rt_scene_set_launch_width(scene_handle, self.ctas_per_sm), lib)
 
     # -- one frame --------------------------------------------------------------------------------
     def submit(self, host_io=False):
@@ -210,6 +214,7 @@ class FramePipeline:
 
     def close(self):
         self.drain()
+        self.lib.rt_scene_set_launch_width(self.scene, 0)
         self.fb_view = self.ctr_view = None
         for p in self._opened:
             self.lib.rt_ipc_close(p)
