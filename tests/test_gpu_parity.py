@@ -165,6 +165,8 @@ def test_dynamic_tail_queue_and_shared_memory(rt, lib, gpu):
         fo = gpu.FrameOut(fb.value, None, None, None)
         counter = ctr.value + 8 * slot                              # a fresh zero counter per frame
         order = list(range(world))[::-1] if slot % 2 else list(range(world))
+        # narrower persistent grids (frames in flight side by side) render the same frame
+        gpu.check(lib.rt_scene_set_launch_width(dev.handle, slot), lib)      # 0 = all slots, 1, 2 CTAs per SM
         for r in order:
             p = host.params(tile=(r, world, chunk), dyn=(dyn_tiles, dyn_chunk, counter), flags=gpu.RT_FLAG_NO_CLEAR)
             gpu.check(lib.rt_render_device(dev.handle, C.byref(host.camera), d_lpos.data_ptr(), d_lcol.data_ptr(),
@@ -172,6 +174,8 @@ def test_dynamic_tail_queue_and_shared_memory(rt, lib, gpu):
         torch.cuda.synchronize()
         got = fbt.cpu().numpy().reshape(H, W, 4)
         assert np.array_equal(got, full)
+    gpu.check(lib.rt_scene_set_launch_width(dev.handle, 0), lib)
+    assert lib.rt_scene_set_launch_width(dev.handle, -1) == gpu.RT_ERR_INVALID_ARG
     # invalid dynamic-queue arguments are rejected
     bad = host.params(dyn=(10, 4, None))
     fo = gpu.FrameOut(fb.value, None, None, None)
