@@ -104,6 +104,10 @@ int adopt_blob(rt_scene *s) {
   s->view.meshes = reinterpret_cast<const MeshRec *>(b + h.off_meshes);
   s->view.objects = reinterpret_cast<const ObjectRec *>(b + h.off_objects);
   s->view.objfilt = reinterpret_cast<const ObjFilter *>(b + h.off_objfilt);
+  s->view.obj_order = reinterpret_cast<const int32_t *>(b + h.off_obj_order);
+  s->view.lin_idx = reinterpret_cast<const int32_t *>(b + h.off_lin_idx);
+  s->view.obj_root = h.obj_root; s->view.num_lin = h.num_lin;
+  s->view.tri_nodes = h.q_base + h.num_nodes_q;
   s->view.texels = reinterpret_cast<const float *>(b + h.off_texels);
   s->view.num_nodes = h.num_nodes; s->view.num_tris = h.num_tris;
   s->view.num_meshes = h.num_meshes; s->view.num_objects = h.num_objects;
@@ -153,16 +157,20 @@ int adopt_blob(rt_scene *s) {
   // throttles the resident CTAs per SM
   s->extra_smem = 0;
   if (const char *e = std::getenv("RT_EXTRA_SMEM")) s->extra_smem = (size_t)std::atol(e);
+  // the two kernel variants this scene uses: plain and instrumented, with or without the object-tree code
+  const bool obj = h.obj_root >= 0;
+  const void *k_plain = obj ? (const void *)render_kernel<K_OBJ> : (const void *)render_kernel<0>;
+  const void *k_count = obj ? (const void *)render_kernel<K_COUNT | K_OBJ> : (const void *)render_kernel<K_COUNT>;
   if (s->extra_smem) {
-    RT_CUDA(cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
-    RT_CUDA(cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+    RT_CUDA(cudaFuncSetAttribute(k_plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+    RT_CUDA(cudaFuncSetAttribute(k_count, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
   }
   if (const char *e = std::getenv("RT_CARVEOUT")) { // experiments only: shared-memory carveout in percent
-    RT_CUDA(cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e)));
-    RT_CUDA(cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e)));
+    RT_CUDA(cudaFuncSetAttribute(k_plain, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e)));
+    RT_CUDA(cudaFuncSetAttribute(k_count, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e)));
   }
-  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, render_kernel<false>, kBlockThreads, s->extra_smem));
-  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, render_kernel<true>, kBlockThreads, s->extra_smem));
+  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, k_plain, kBlockThreads, s->extra_smem));
+  RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_count, kBlockThreads, s->extra_smem));
   s->sm_count = prop.multiProcessorCount;
   s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
   s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
@@ -215,8 +223,14 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
     gc = gc < lim ? gc : lim;
     gp = gp < lim ? gp : lim;
   }
-  if (count) render_kernel<true><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
-  else render_kernel<false><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
+  const bool obj = s->hdr.obj_root >= 0; // tree over analytic spheres: the kernel variant that can walk it
+  if (count) {
+    if (obj) render_kernel<K_COUNT | K_OBJ><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
+    else render_kernel<K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
+  } else {
+    if (obj) render_kernel<K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
+    else render_kernel<0><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
+  }
   RT_CUDA(cudaGetLastError());
   RT_CUDA(cudaEventRecord(s->ev1[slot], st));
   s->timed = true;

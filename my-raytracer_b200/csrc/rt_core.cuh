@@ -76,8 +76,15 @@ struct Hot {
   int sp;
   int mode;
   int found;   // any-hit result
-  int xpar;    // direction.x == 0 exactly: the reference's 0/0 slab quirk applies (rt_types.h NodeMaxX)
+  int special; // rare-path flags, tested with ONE predicate in the hot loop:
+               //   S_XPAR: direction.x == 0 exactly, the reference's 0/0 slab quirk applies (rt_types.h NodeMaxX)
+               //   S_OBJ : the ray is walking the tree over the analytic spheres (before the triangle tree)
 };
+enum Special : int { S_XPAR = 1, S_OBJ = 2 };
+// Kernel configuration bits (the template parameter named COUNT throughout): K_COUNT = instrumented build,
+// K_OBJ = the scene has a tree over analytic spheres.  Scenes without one run a kernel that contains none of
+// that code (its mere presence in the leaf path costs 3 % on the Office scene).
+enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2 };
 
 struct Mat {
   D3 ka, ks;
@@ -147,8 +154,8 @@ RT_HD W8 ld_w8(const void *p) {
 }
 RT_HD float w2f(unsigned u) { return __int_as_float_rt((int)u); }
 
-template <bool COUNT> RT_HD void bump(const Ctx &c, int which, unsigned n = 1) {
-  if (COUNT) c.cnt[which] += n;
+template <int COUNT> RT_HD void bump(const Ctx &c, int which, unsigned n = 1) {
+  if (COUNT & K_COUNT) c.cnt[which] += n;
 }
 
 RT_HD void load_mat(const SceneView &sv, int mat, Mat &m) {
@@ -179,7 +186,27 @@ RT_HD D3 fetch_texel(const SceneView &sv, int mesh, const MeshRec &mr, int px, i
 // ray start: Ray(origin, dir) normalises dir (oracle/shim/utils/Ray.h), then the analytic
 // primitives are tested in list order (restated intersect_scene), then the BVH is entered.
 // ---------------------------------------------------------------------------------------
-template <bool COUNT, int S>
+// Enter the triangle tree: ordinary rays walk the traversal tree (records from 0), rays with d.x == 0 the
+// reference's own tree (records from q_base; the same tree when q_base == 0): only there does the 0/0 slab
+// quirk apply.
+template <int S> RT_HD void enter_triangles(const Ctx &c, Hot &H, const Cold<S> &C) {
+  const SceneView &sv = c.sv;
+  H.special &= S_XPAR;
+  H.sp = 0;
+  H.node = (sv.tri_nodes > 0) ? (H.special ? sv.q_base : 0) : -1;
+  // root box, tested on entry by the reference (mybvh.cpp:157): (bb_max.x - o.x)/0 = NaN rejects it
+  if (H.special && C.d(CD_O) == sv.root_max_x) H.node = -1;
+}
+
+// The ray's current tree is exhausted (node < 0).  Returns true if it moved on to the next tree.
+template <int COUNT, int S> RT_HD bool next_tree(const Ctx &c, Hot &H, const Cold<S> &C) {
+  if (!(COUNT & K_OBJ) || !(H.special & S_OBJ) || H.mode == M_IDLE) return false;
+  if (H.found) { H.special &= S_XPAR; return false; } // any-hit ray already occluded by a sphere
+  enter_triangles(c, H, C);
+  return H.node >= 0;
+}
+
+template <int COUNT, int S>
 RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, const D3 &dir, int mode, double tmax) {
   const D3 o = origin;
   const D3 d = normalize(dir);
@@ -194,7 +221,8 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   float othi = thi_of(best);
   const bool exact_only = (c.fp.flags & 1) != 0;
   const SceneView &sv = c.sv;
-  for (int k = 0; k < sv.num_objects; ++k) {
+  for (int q = 0; q < sv.num_lin; ++q) {
+    const int k = sv.lin_idx[q];
     double t;
     bump<COUNT>(c, C_OBJECT);
     // FP32 pre-filter on the 32-byte ObjFilter record (a 4-wide batched variant of this loop was measured and is
@@ -217,17 +245,19 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   C.d(CD_BEST_T) = best;
   H.thi = thi_of(best);
   H.thiS = this_of(H.thi);
-  H.xpar = (d.x == 0.0);
-  // ordinary rays walk the traversal tree (records from 0), rays with d.x == 0 the reference's own tree
-  // (records from q_base; the same tree when q_base == 0): only there does the 0/0 slab quirk apply
-  H.node = (sv.num_nodes > 0) ? (H.xpar ? sv.q_base : 0) : -1;
-  // root box, tested on entry by the reference (mybvh.cpp:157): (bb_max.x - o.x)/0 = NaN rejects it
-  if (H.xpar && o.x == sv.root_max_x) H.node = -1;
+  H.special = (d.x == 0.0) ? S_XPAR : 0;
+  if ((COUNT & K_OBJ) && sv.obj_root >= 0) {
+    // spheres first (the reference tests objects_ before the meshes): walk their tree, then the triangles
+    H.special |= S_OBJ;
+    H.node = sv.obj_root;
+  } else {
+    enter_triangles(c, H, C);
+  }
 }
 
 // FP64 confirmation of one filter survivor + nearest / any-hit bookkeeping.  Rare (~0.7 per ray).
 // j: position in traversal order (TriExact index); the reported / tie-breaking id is tri_id[j].
-template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const Cold<S> &C, int j) {
+template <int COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const Cold<S> &C, int j) {
   bump<COUNT>(c, C_TRI_EXACT);
   const TriExact &e = c.sv.exact[j];
   TriHit h;
@@ -251,16 +281,49 @@ template <bool COUNT, int S> RT_HD void confirm_tri(const Ctx &c, Hot &H, const 
   }
 }
 
+// Spheres [first, last) of a leaf of the object tree (positions of obj_order).  Same decisions as the linear
+// loop of start_ray: exact FP64 test, strict '<', and on equal t the lower object index wins — the reference
+// tests objects_ in list order, so the first of two equal hits is kept.
+template <int COUNT, int S>
+RT_HD void obj_leaf(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last, bool exact_only) {
+  const SceneView &sv = c.sv;
+  for (int q = first; q < last; ++q) {
+    const int k = sv.obj_order[q];
+    bump<COUNT>(c, C_OBJECT);
+    const char *fp = reinterpret_cast<const char *>(sv.objfilt + k);
+    const F4 f0 = ld_f4(fp);
+    const I4 f1 = ld_i4(fp + 16);
+    const float fc[3] = {f0.x, f0.y, f0.z};
+    if (!exact_only && !sphere_filter(H.rf, fc, f0.w, __int_as_float_rt(f1.x), H.thi)) continue;
+    const ObjectRec &ob = sv.objects[k];
+    double t;
+    if (!sphere_exact(C.v(CD_O), C.v(CD_D), ld3(ob.center), ob.radius, t)) continue;
+    const double best = C.d(CD_BEST_T);
+    const int id = sv.num_tris + k;
+    if (H.mode == M_ANYHIT) {
+      if (t < best) { H.found = 1; H.node = -1; return; }
+      continue;
+    }
+    if (t < best || (t == best && H.best_id >= sv.num_tris && id < H.best_id)) {
+      C.d(CD_BEST_T) = t;
+      H.best_id = id;
+      H.thi = thi_of(t);
+      H.thiS = this_of(H.thi);
+    }
+  }
+}
+
 // Triangles [first, last) of one leaf — or of two sibling leaves, whose ranges are adjacent (rt_types.h).
 // Leaves of the traversal tree hold positions of the triangle records; leaves of the reference tree (walked
 // by d.x == 0 rays only) hold reference primitive indices, mapped through tri_pos.
-template <bool COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last) {
+template <int COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last) {
   const bool exact_only = (c.fp.flags & 1) != 0;
+  if ((COUNT & K_OBJ) && (H.special & S_OBJ)) { obj_leaf<COUNT>(c, H, C, first, last, exact_only); return; }
   for (int k = first; k < last; ++k) {
     bump<COUNT>(c, C_TRI_FILTER);
     bool pass = exact_only;
     int i = k;
-    if (H.xpar) i = c.sv.tri_pos[k];
+    if (H.special) i = c.sv.tri_pos[k];
     if (!exact_only) {
       const char *p = reinterpret_cast<const char *>(c.sv.filt + i);
       const F4 a = ld_f4(p), b = ld_f4(p + 16), d = ld_f4(p + 32);
@@ -288,7 +351,7 @@ struct alignas(8) StackEntry {
 // The kernel calls this from a WARP-UNIFORM loop (while (__any_sync(node >= 0)) if (node >= 0) step):
 // the vote re-converges the warp every iteration.  A per-lane `while (node >= 0)` loop lets lanes
 // drift out of phase and ran 2x slower on B200 (profiles/r01_variants.md).
-template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
+template <int COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   const char *np = reinterpret_cast<const char *>(c.sv.nodes) + (size_t)(unsigned)H.node * 64u;
   const W8 lo = ld_w8(np), hi = ld_w8(np + 32);   // two 32-byte loads per 64-byte record
   I4 r; r.x = (int)hi.w[4]; r.y = (int)hi.w[5]; r.z = (int)hi.w[6]; r.w = (int)hi.w[7];
@@ -300,7 +363,7 @@ template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Co
   float tn0, tn1;
   bool h0 = box_test(H.rf, b0c, b0h, H.thiS, tn0);
   bool h1 = box_test(H.rf, b1c, b1h, H.thiS, tn1);
-  if (H.xpar) { // rare (exactly axis-parallel rays): reproduce the reference's NaN rejection
+  if (H.special == S_XPAR) { // rare (exactly axis-parallel rays in the reference tree): reproduce its NaN rejection
     const NodeMaxX mx = c.sv.maxx[H.node - c.sv.q_base];
     const double ox = C.d(CD_O);
     h0 = h0 && !(ox == mx.c0_max_x);
@@ -337,14 +400,16 @@ template <bool COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Co
 }
 
 // host/test build: run this lane's ray to completion
-template <bool COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
-  while (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
+template <int COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
+  do {
+    while (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
+  } while (next_tree<COUNT>(c, H, C));
 }
 
 // ---------------------------------------------------------------------------------------
 // path logic (cold: FP64, runs once per ray, not per node)
 // ---------------------------------------------------------------------------------------
-template <bool COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const Cold<S> &C) {
+template <int COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const Cold<S> &C) {
   const CameraRec &cam = c.fp.cam;
   double x = (double)C.i(CI_PX), y = (double)C.i(CI_PY);
   const int s = c.fp.spp_grid;
@@ -388,7 +453,7 @@ template <int S> RT_HD void write_pixel(const Ctx &c, const Cold<S> &C) {
   }
 }
 
-template <bool COUNT, int S> RT_HD void sample_done(const Ctx &c, Hot &H, const Cold<S> &C) {
+template <int COUNT, int S> RT_HD void sample_done(const Ctx &c, Hot &H, const Cold<S> &C) {
   C.set(CD_ACC, add(C.v(CD_ACC), C.v(CD_COL)));
   const int sample = C.i(CI_SAMPLE) + 1;
   C.i(CI_SAMPLE) = sample;
@@ -402,7 +467,7 @@ template <bool COUNT, int S> RT_HD void sample_done(const Ctx &c, Hot &H, const 
 }
 
 // Fill P, N, V, kd, mat for the nearest hit and start the lighting loop (L = ambient term).
-template <bool COUNT, int S> RT_HD void hit_setup(const Ctx &c, Hot &H, const Cold<S> &C, Mat &m) {
+template <int COUNT, int S> RT_HD void hit_setup(const Ctx &c, Hot &H, const Cold<S> &C, Mat &m) {
   const SceneView &sv = c.sv;
   const D3 o = C.v(CD_O), d = C.v(CD_D);
   const double best = C.d(CD_BEST_T);
@@ -488,7 +553,7 @@ template <int S> RT_HD void add_light(const Ctx &c, const Cold<S> &C, const Mat 
 }
 
 // Advance a lane whose traversal has finished until it has a new ray in flight or is idle.
-template <bool COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<S> &C) {
+template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<S> &C) {
   const SceneView &sv = c.sv;
   while (H.mode != M_IDLE && H.node < 0) {
     Mat m;
@@ -556,7 +621,7 @@ template <bool COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold
 }
 
 // Begin a pixel (lane must be idle).
-template <bool COUNT, int S> RT_HD void begin_pixel(const Ctx &c, Hot &H, const Cold<S> &C, int px, int py) {
+template <int COUNT, int S> RT_HD void begin_pixel(const Ctx &c, Hot &H, const Cold<S> &C, int px, int py) {
   C.i(CI_PX) = px;
   C.i(CI_PY) = py;
   C.i(CI_SAMPLE) = 0;

@@ -28,6 +28,8 @@ inline float round_up(double v) {
 }
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+constexpr int kObjTreeMin = 8; // spheres: below this the linear per-ray loop stays
+
 struct Walk {
   int ref_node;  // node index in the reference arrays
   int flat_idx;  // NodeRec index assigned to it
@@ -376,6 +378,75 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     q.r = r.rf; q.cabs = r.cabs; q.kind = r.kind;
   }
 
+  // ---- 3b. object tree: SAH over the spheres' boxes when the linear per-ray loop would dominate ----------
+  std::vector<int32_t> obj_order, lin_idx;
+  int obj_root = -1, num_nodes_obj = 0;
+  {
+    std::vector<int> sph;
+    for (int k = 0; k < num_objects; ++k)
+      if (objs[k].kind == RT_SPHERE && std::isfinite(objs[k].radius) && objs[k].radius >= 0.0) sph.push_back(k);
+    const int ns = (int)sph.size();
+    bool built = false;
+    if (ns >= kObjTreeMin && !(flags & RT_SCENE_REFERENCE_TOPOLOGY)) {
+      std::vector<float> plo(3 * (size_t)ns), phi(3 * (size_t)ns);
+      for (int j = 0; j < ns; ++j) {
+        const ObjectRec &o = objs[sph[j]];
+        for (int a = 0; a < 3; ++a) {
+          // one ulp of FP64 slack on each side before the outward FP32 rounding: covers the rounding of c -+ r
+          plo[3 * (size_t)j + a] = round_down(std::nextafter(o.center[a] - o.radius, -std::numeric_limits<double>::infinity()));
+          phi[3 * (size_t)j + a] = round_up(std::nextafter(o.center[a] + o.radius, std::numeric_limits<double>::infinity()));
+        }
+      }
+      std::vector<int> order;
+      std::vector<SahNode> sn;
+      int depth = 0;
+      build_sah(plo.data(), phi.data(), ns, order, sn, depth);
+      if (!sn.empty() && sn[0].count == 0 && depth <= kStackMax) {
+        const int base = (int)nodes.size();
+        std::vector<NodeRec> trav;
+        std::vector<Walk> todo;
+        trav.emplace_back();
+        todo.push_back({0, 0, 1});
+        while (!todo.empty()) {
+          const Walk w = todo.back();
+          todo.pop_back();
+          const SahNode &sp = sn[w.ref_node];
+          const int ch[2] = {sp.left, sp.right};
+          NodeRec n;
+          int ref[2], cnt[2], child_flat[2] = {-1, -1};
+          for (int s2 = 0; s2 < 2; ++s2) {
+            const SahNode &cn = sn[ch[s2]];
+            const double lo[3] = {cn.lo[0], cn.lo[1], cn.lo[2]}, hi[3] = {cn.hi[0], cn.hi[1], cn.hi[2]};
+            box_lohi(lo, hi, s2 ? n.c1_ctr : n.c0_ctr, s2 ? n.c1_half : n.c0_half);
+            if (cn.count > 0) { ref[s2] = cn.first; cnt[s2] = cn.count; }
+            else {
+              child_flat[s2] = (int)trav.size();
+              trav.emplace_back();
+              ref[s2] = base + child_flat[s2]; cnt[s2] = 0;
+            }
+          }
+          if (child_flat[1] >= 0) todo.push_back({ch[1], child_flat[1], w.depth + 1});
+          if (child_flat[0] >= 0) todo.push_back({ch[0], child_flat[0], w.depth + 1});
+          n.ref0 = ref[0]; n.cnt0 = cnt[0]; n.ref1 = ref[1]; n.cnt1 = cnt[1];
+          trav[w.flat_idx] = n;
+        }
+        if (depth > max_depth) max_depth = depth;
+        obj_root = base;
+        num_nodes_obj = (int)trav.size();
+        nodes.insert(nodes.end(), trav.begin(), trav.end());
+        obj_order.resize(ns);
+        for (int j = 0; j < ns; ++j) obj_order[j] = sph[order[j]];
+        std::vector<unsigned char> in_tree(num_objects, 0);
+        for (int k : sph) in_tree[k] = 1;
+        for (int k = 0; k < num_objects; ++k)
+          if (!in_tree[k]) lin_idx.push_back(k);
+        built = true;
+      }
+    }
+    if (!built)
+      for (int k = 0; k < num_objects; ++k) lin_idx.push_back(k);
+  }
+
   // ---- 4. assemble -----------------------------------------------------------------------------
   BlobHeader h;
   std::memset(&h, 0, sizeof(h));
@@ -397,6 +468,9 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.off_tri_id = off;  off = align_up(off + tri_id.size() * sizeof(int32_t), kSectionAlign);
   h.off_tri_pos = off; off = align_up(off + tri_pos.size() * sizeof(int32_t), kSectionAlign);
   h.off_objfilt = off; off = align_up(off + objf.size() * sizeof(ObjFilter), kSectionAlign);
+  h.off_obj_order = off; off = align_up(off + obj_order.size() * sizeof(int32_t), kSectionAlign);
+  h.off_lin_idx = off; off = align_up(off + lin_idx.size() * sizeof(int32_t), kSectionAlign);
+  h.obj_root = obj_root; h.num_nodes_obj = num_nodes_obj; h.num_obj_tree = (int)obj_order.size(); h.num_lin = (int)lin_idx.size();
   h.q_base = q_base; h.num_nodes_q = num_nodes_q; h.topology = topology;
   h.root_max_x = N > 0 ? bvh->bb_max_[0].x : 0.0;
   h.total_bytes = off;
@@ -414,6 +488,8 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   if (num_meshes > 0) std::memcpy(blob.data() + h.off_meshes, meshes.data(), meshes.size() * sizeof(MeshRec));
   if (num_objects > 0) std::memcpy(blob.data() + h.off_objects, objs.data(), objs.size() * sizeof(ObjectRec));
   if (num_objects > 0) std::memcpy(blob.data() + h.off_objfilt, objf.data(), objf.size() * sizeof(ObjFilter));
+  if (!obj_order.empty()) std::memcpy(blob.data() + h.off_obj_order, obj_order.data(), obj_order.size() * sizeof(int32_t));
+  if (!lin_idx.empty()) std::memcpy(blob.data() + h.off_lin_idx, lin_idx.data(), lin_idx.size() * sizeof(int32_t));
   float *tx = reinterpret_cast<float *>(blob.data() + h.off_texels);
   for (size_t t = 0; t < num_texels; ++t) {
     const rt_vec4 &c = data->meshTexels_[t];
@@ -438,8 +514,12 @@ int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
                   h.off_maxx + (size_t)h.num_nodes_q * sizeof(NodeMaxX) <= h.off_tri_id &&
                   h.off_tri_id + (size_t)h.num_tris * sizeof(int32_t) <= h.off_tri_pos &&
                   h.off_tri_pos + (size_t)h.num_tris * sizeof(int32_t) <= h.off_objfilt &&
-                  h.off_objfilt + (size_t)h.num_objects * sizeof(ObjFilter) <= h.total_bytes &&
-                  h.q_base >= 0 && h.num_nodes_q >= 0 && (size_t)h.q_base + (size_t)h.num_nodes_q == (size_t)h.num_nodes;
+                  h.off_objfilt + (size_t)h.num_objects * sizeof(ObjFilter) <= h.off_obj_order &&
+                  h.off_obj_order + (size_t)h.num_obj_tree * sizeof(int32_t) <= h.off_lin_idx &&
+                  h.off_lin_idx + (size_t)h.num_lin * sizeof(int32_t) <= h.total_bytes &&
+                  h.num_nodes_obj >= 0 && h.num_obj_tree >= 0 && h.num_lin >= 0 && h.num_obj_tree + h.num_lin == h.num_objects &&
+                  (h.obj_root < 0 ? h.num_nodes_obj == 0 : h.obj_root == h.q_base + h.num_nodes_q) &&
+                  h.q_base >= 0 && h.num_nodes_q >= 0 && (size_t)h.q_base + (size_t)h.num_nodes_q + (size_t)h.num_nodes_obj == (size_t)h.num_nodes;
   if (!ok) { err = "blob: section table inconsistent"; return RT_ERR_BAD_SCENE; }
   return RT_OK;
 }
@@ -455,6 +535,10 @@ SceneView view_of_blob(const unsigned char *blob) {
   v.meshes = reinterpret_cast<const MeshRec *>(blob + h.off_meshes);
   v.objects = reinterpret_cast<const ObjectRec *>(blob + h.off_objects);
   v.objfilt = reinterpret_cast<const ObjFilter *>(blob + h.off_objfilt);
+  v.obj_order = reinterpret_cast<const int32_t *>(blob + h.off_obj_order);
+  v.lin_idx = reinterpret_cast<const int32_t *>(blob + h.off_lin_idx);
+  v.obj_root = h.obj_root; v.num_lin = h.num_lin;
+  v.tri_nodes = h.q_base + h.num_nodes_q; v.pad_v = 0;
   v.texels = reinterpret_cast<const float *>(blob + h.off_texels);
   v.tex_objs = nullptr;
   v.maxx = reinterpret_cast<const NodeMaxX *>(blob + h.off_maxx);

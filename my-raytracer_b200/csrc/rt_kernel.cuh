@@ -44,10 +44,10 @@ struct KernelArgs {
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 4
 #endif
-template <bool COUNT>
+template <int COUNT>
 __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(const __grid_constant__ KernelArgs a) {
-  unsigned int cnt[COUNT ? C_COUNT : 1];
-  if (COUNT) {
+  unsigned int cnt[(COUNT & K_COUNT) ? C_COUNT : 1];
+  if (COUNT & K_COUNT) {
 #pragma unroll
     for (int k = 0; k < C_COUNT; ++k) cnt[k] = 0;
   }
@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
   H.sp = 0;
   H.found = 0;
   H.best_id = -1;
-  H.xpar = 0;
+  H.special = 0;
   const long long slots = work_slots(c);
   const long long nchunks = a.dyn_counter ? pool_chunks(c) : 0;
   const unsigned lane = threadIdx.x & 31u;
@@ -168,11 +168,16 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     // (Leaving the loop early to refill finished lanes was measured and is a loss: lanes of one warp then
     // work on rays of different generations, the node loads stop coalescing and the shading code runs at
     // low lane counts — 10.8-17 ms instead of 7.2, profiles/r01_variants.md.)
-    while (__any_sync(kFullMask, H.node >= 0)) {
-      if (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
+    for (;;) {
+      while (__any_sync(kFullMask, H.node >= 0)) {
+        if (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
+      }
+      // rays that finished the tree over the analytic spheres move on to the triangle tree (rt_core.cuh)
+      if (!(COUNT & K_OBJ)) break;
+      if (!__any_sync(kFullMask, next_tree<COUNT>(c, H, C))) break;
     }
   }
-  if (COUNT) {
+  if (COUNT & K_COUNT) {
 #pragma unroll
     for (int k = 0; k < C_COUNT; ++k)
       if (cnt[k]) atomicAdd(a.counters + k, (unsigned long long)cnt[k]);
@@ -180,7 +185,7 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
 #ifdef RT_TAILPROBE
   // experiment (tools/gpu_tailprobe.py): when does each warp run out of work?  counters[0] = sum of
   // warp end times, [1] = max, [2] = min start, [3] = number of warps (globaltimer ns)
-  if (!COUNT && lane == 0) {
+  if (!(COUNT & K_COUNT) && lane == 0) {
     unsigned long long t1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
     atomicAdd(a.counters + 0, t1 - t_probe0);

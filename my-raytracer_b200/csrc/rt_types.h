@@ -6,7 +6,8 @@
 //   BlobHeader | NodeRec[] | TriFilter[] | TriExact[] | TriShade[] | MeshRec[] | ObjectRec[] | texels | NodeMaxX[]
 //              | tri_id[] | tri_pos[] | ObjFilter[]
 //
-// Two trees share the NodeRec array (rt_sah.h): records [0, q_base) are the product's SAH traversal tree,
+// Up to three trees share the NodeRec array (rt_sah.h); the third, over the analytic spheres of
+// Raytracer::objects_ (the reference loops over them linearly per ray), is walked before the triangles: records [0, q_base) are the product's SAH traversal tree,
 // records [q_base, q_base + num_nodes_q) the reference's median-split tree, walked only by rays with
 // direction.x == 0 (NodeMaxX below).  With RT_SCENE_REFERENCE_TOPOLOGY there is one tree (q_base == 0) and
 // every ray walks the reference topology.  TriFilter / TriExact are stored in the leaf order of the traversal
@@ -40,7 +41,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 7;
+constexpr uint32_t kBlobVersion = 8;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -136,6 +137,12 @@ struct BlobHeader {
   int32_t topology;    // 0 SAH traversal tree + reference tree, 1 reference tree only
   int32_t pad_i;
   uint64_t off_objfilt; // ObjFilter[num_objects]
+  // analytic primitives: spheres go into a third tree (records [obj_base, obj_base + num_nodes_obj)) when there
+  // are enough of them; everything else (planes; all objects when there is no tree) is tested linearly per ray
+  uint64_t off_obj_order; // int32[num_obj_tree]: leaf position -> object index
+  uint64_t off_lin_idx;   // int32[num_lin]: objects tested linearly, in list order
+  int32_t obj_root;       // record index of the object tree's root, -1: no object tree
+  int32_t num_nodes_obj, num_obj_tree, num_lin;
   uint64_t reserved[1];
 };
 static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
@@ -154,6 +161,11 @@ struct SceneView {
   const NodeMaxX *maxx;
   const int32_t *tri_id;  // traversal-order position -> reference primitive index
   const int32_t *tri_pos; // reference primitive index -> traversal-order position
+  const int32_t *obj_order; // object-tree leaf position -> object index
+  const int32_t *lin_idx;   // objects tested linearly at ray start
+  int32_t obj_root, num_lin;
+  int32_t tri_nodes;        // records of the triangle trees (0: the scene has no triangles)
+  int32_t pad_v;
   double root_max_x;
   int32_t num_nodes, num_tris, num_meshes, num_objects;
   float box_extent;

@@ -482,5 +482,30 @@ def mixed_small(width=160, height=120, seed=1):
     return SceneDesc("mixed_small", meshes, objs, lights, cam, (0.05, 0.05, 0.1), (0.2, 0.2, 0.2), 4)
 
 
-REGISTRY = {"spheres": spheres, "office": office, "molecule": molecule, "rings": rings, "textured": textured,
+def objtree(width=96, height=72, seed=11, camera_inside=True):
+    """Enough analytic spheres for the object tree (>= 8), with the cases that test the reference's list-order
+    semantics: a plane in the middle of the list, an exact duplicate of object 1 at a higher index (equal t: the
+    lower index must win), a sphere with the geometry of object 5 and another material, optionally a sphere around
+    the camera (ray origins inside a box and inside a sphere), and a triangle mesh behind everything."""
+    rng = np.random.default_rng(seed)
+
+    def mat(c, mirror=0.0):
+        return material((0.1, 0.1, 0.1), c, (0.5, 0.5, 0.5), 30.0, mirror)
+    objs = []
+    for k in range(14):
+        ctr = tuple(rng.uniform(-2.0, 2.0, 3) * np.array([1.0, 0.6, 1.0]))
+        objs.append(("sphere", ctr, float(rng.uniform(0.25, 0.7)), mat(tuple(rng.uniform(0.2, 1.0, 3)), 0.3 if k % 4 == 0 else 0.0)))
+    objs.insert(3, ("plane", (0.0, -1.5, 0.0), (0.0, 1.0, 0.0), mat((0.7, 0.7, 0.7), 0.2)))
+    objs.append(objs[1])
+    objs.append(("sphere", objs[5][1], objs[5][2], mat((1.0, 0.0, 1.0))))
+    if camera_inside:
+        objs.append(("sphere", (0.0, 0.0, 6.0), 1.5, mat((0.2, 0.9, 0.9))))
+    quad = grid_quad((-3.0, -1.0, -4.0), (6.0, 0.0, 0.0), (0.0, 4.0, 0.0), 6, 4)
+    return SceneDesc("objtree", [MeshDesc(quad[0], quad[1], mat((0.9, 0.8, 0.3)))], objs,
+                     [((3.0, 4.0, 5.0), (0.8, 0.8, 0.8)), ((-4.0, 2.0, 1.0), (0.5, 0.5, 0.6))],
+                     dict(eye=(0.0, 0.0, 6.0), center=(0.0, 0.0, 0.0), up=(0, 1, 0), fovy=50, width=width, height=height),
+                     ambience=(0.2, 0.2, 0.2), max_depth=3)
+
+
+REGISTRY = {"objtree": objtree, "spheres": spheres, "office": office, "molecule": molecule, "rings": rings, "textured": textured,
             "scatter": scatter, "mixed_small": mixed_small}

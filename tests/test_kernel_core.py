@@ -222,6 +222,7 @@ def test_axis_parallel_rays_reproduce_reference_nan_quirk(rt, lib, sim, orc, ora
 @pytest.mark.parametrize("scene,kw", [("mixed_small", dict(width=96, height=72)),
                                       ("scatter", dict(width=64, height=36, n_objects=40)),
                                       ("rings", dict(width=70, height=50, nu=48, nv=16)),
+                                      ("molecule", dict(width=90, height=90, n_spheres=150)),
                                       ("textured", dict(width=96, height=54, tex_size=64, slices=24, stacks=12))])
 def test_frame_does_not_depend_on_the_tree(rt, lib, sim, scene, kw):
     """The library's own SAH traversal tree and the reference's median-split topology give bit-identical frames
@@ -232,4 +233,36 @@ def test_frame_does_not_depend_on_the_tree(rt, lib, sim, scene, kw):
     b = sim.render(host, sim.flatten(host))
     for k in ("hit_id", "hit_t", "rgba8", "pixels"):
         assert np.array_equal(a[k], b[k]), k
-    assert b["counters"]["nodes_visited"] < a["counters"]["nodes_visited"]
+    if host.num_triangles:
+        assert b["counters"]["nodes_visited"] < a["counters"]["nodes_visited"]
+    else:       # analytic-only scene: the tree over the spheres replaces most of the per-ray object tests
+        assert b["counters"]["object_tests"] < 0.5 * a["counters"]["object_tests"]
+
+
+def test_object_tree_keeps_list_order_semantics(rt, lib, sim, orc, oracle_kind):
+    """Spheres go into their own tree when there are >= 8 of them; the reference loops over objects_ in list order
+    with a strict '<'.  Duplicated spheres (equal t: the lower index must win), a sphere around the camera (ray
+    origins inside a box and inside a sphere), planes between them in the list, and triangles behind: ids,
+    distances and pixels equal the oracle's and the linear loop's."""
+    desc = rt.scenes.objtree()
+    objs = desc.objects
+    host = rt.HostScene(desc, lib)
+    tree = sim.render(host, sim.flatten(host))
+    lin = sim.render(host, sim.flatten(host, rt.capi.RT_SCENE_REFERENCE_TOPOLOGY))
+    ref = orc.OracleScene(desc, oracle_kind).render()
+    for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+        assert np.array_equal(tree[k], lin[k]), k
+    assert np.array_equal(tree["hit_id"], ref["ids"]) and np.array_equal(tree["hit_t"], ref["t"])
+    assert np.abs(tree["pixels"][..., :3] - ref["rgb"]).max() < 1e-9
+    n = desc.num_triangles
+    assert (tree["hit_id"] == n + len(objs) - 1).all()             # every primary ray starts inside the last sphere...
+    assert tree["counters"]["nodes_visited"] > 0 and tree["counters"]["object_tests"] < lin["counters"]["object_tests"]
+    # the same scene seen from outside: duplicates and shared geometry decide visible pixels
+    desc = rt.scenes.objtree(camera_inside=False)
+    host = rt.HostScene(desc, lib)
+    tree = sim.render(host, sim.flatten(host))
+    ref = orc.OracleScene(desc, oracle_kind).render()
+    assert np.array_equal(tree["hit_id"], ref["ids"]) and np.array_equal(tree["hit_t"], ref["t"])
+    assert np.abs(tree["pixels"][..., :3] - ref["rgb"]).max() < 1e-9
+    ids = set(np.unique(tree["hit_id"]).tolist())
+    assert n + 1 in ids and n + 15 not in ids and n + 5 in ids and n + 16 not in ids   # the first of two equal hits is kept
