@@ -154,6 +154,7 @@ typedef struct rt_counters {
   unsigned long long nodes_visited;  /* interior node records loaded */
   unsigned long long shadow_trivial; /* shadow rays (counted in rays_shadow) resolved without traversal:
                                         the light's contribution is exactly zero whatever the occlusion */
+  unsigned long long shadow_occluded;   /* shadow rays that found an occluder */
 } rt_counters;
 
 typedef struct rt_scene_info {

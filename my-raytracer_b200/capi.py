@@ -94,7 +94,8 @@ class FrameOut(C.Structure):
 class Counters(C.Structure):
     _fields_ = [(n, C.c_ulonglong) for n in (
         "rays_primary", "rays_shadow", "rays_reflect", "box_tests", "tri_filter", "tri_exact",
-        "object_tests", "shaded_hits", "texel_fetches", "nodes_visited", "shadow_trivial")]
+        "object_tests", "shaded_hits", "texel_fetches", "nodes_visited", "shadow_trivial",
+        "shadow_occluded")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}

@@ -247,6 +247,7 @@ int fetch_counters(rt_scene *s, cudaStream_t st) {
   c.object_tests = h[C_OBJECT]; c.shaded_hits = h[C_SHADED]; c.texel_fetches = h[C_TEXEL];
   c.nodes_visited = h[C_NODES];
   c.shadow_trivial = h[C_SHADOW_TRIVIAL];
+  c.shadow_occluded = h[C_SHADOW_OCCLUDED];
   return RT_OK;
 }
 

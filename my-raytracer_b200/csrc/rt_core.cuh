@@ -573,6 +573,7 @@ template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<
     } else { // M_ANYHIT finished: CI_LIGHT was the light under test
       load_mat(sv, C.i(CI_MAT), m);
       if (!H.found) add_light(c, C, m, C.i(CI_LIGHT), true);
+      else bump<COUNT>(c, C_SHADOW_OCCLUDED);
       C.i(CI_LIGHT) = C.i(CI_LIGHT) + 1;
     }
     H.mode = M_SHADE;

@@ -200,7 +200,7 @@ struct FrameOut {
 // indices into the counters array (RT_FLAG_COUNTERS build)
 enum Counter {
   C_RAY_PRIMARY = 0, C_RAY_SHADOW, C_RAY_REFLECT, C_BOX, C_TRI_FILTER, C_TRI_EXACT, C_OBJECT,
-  C_SHADED, C_TEXEL, C_NODES, C_SHADOW_TRIVIAL, C_COUNT
+  C_SHADED, C_TEXEL, C_NODES, C_SHADOW_TRIVIAL, C_SHADOW_OCCLUDED, C_COUNT
 };
 
 } // namespace rtb
