@@ -186,6 +186,13 @@ RT_HD D3 fetch_texel(const SceneView &sv, int mesh, const MeshRec &mr, int px, i
 // ray start: Ray(origin, dir) normalises dir (oracle/shim/utils/Ray.h), then the analytic
 // primitives are tested in list order (restated intersect_scene), then the BVH is entered.
 // ---------------------------------------------------------------------------------------
+// Rays with d.x == 0 walk the reference tree with the full-featured step (trav_step<.., true>); so that the
+// common step carries none of that code (predicated-off instructions still issue: it cost 11 of 70 issue slots
+// per step), such a lane's node is PARKED (encoded <= -2) while the warp runs the common loop and released for a
+// second loop afterwards (rt_kernel.cuh).
+RT_HD int park(int node) { return -2 - node; }
+RT_HD void unpark(int &node) { if (node <= -2) node = -2 - node; }
+
 // Enter the triangle tree: ordinary rays walk the traversal tree (records from 0), rays with d.x == 0 the
 // reference's own tree (records from q_base; the same tree when q_base == 0): only there does the 0/0 slab
 // quirk apply.
@@ -193,7 +200,7 @@ template <int S> RT_HD void enter_triangles(const Ctx &c, Hot &H, const Cold<S> 
   const SceneView &sv = c.sv;
   H.special &= S_XPAR;
   H.sp = 0;
-  H.node = (sv.tri_nodes > 0) ? (H.special ? sv.q_base : 0) : -1;
+  H.node = (sv.tri_nodes > 0) ? (H.special ? park(sv.q_base) : 0) : -1;
   // root box, tested on entry by the reference (mybvh.cpp:157): (bb_max.x - o.x)/0 = NaN rejects it
   if (H.special && C.d(CD_O) == sv.root_max_x) H.node = -1;
 }
@@ -203,7 +210,7 @@ template <int COUNT, int S> RT_HD bool next_tree(const Ctx &c, Hot &H, const Col
   if (!(COUNT & K_OBJ) || !(H.special & S_OBJ) || H.mode == M_IDLE) return false;
   if (H.found) { H.special &= S_XPAR; return false; } // any-hit ray already occluded by a sphere
   enter_triangles(c, H, C);
-  return H.node >= 0;
+  return H.node != -1;
 }
 
 template <int COUNT, int S>
@@ -316,14 +323,14 @@ RT_HD void obj_leaf(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last,
 // Triangles [first, last) of one leaf — or of two sibling leaves, whose ranges are adjacent (rt_types.h).
 // Leaves of the traversal tree hold positions of the triangle records; leaves of the reference tree (walked
 // by d.x == 0 rays only) hold reference primitive indices, mapped through tri_pos.
-template <int COUNT, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last) {
+template <int COUNT, bool XP, int S> RT_HD void leaf_test(const Ctx &c, Hot &H, const Cold<S> &C, int first, int last) {
   const bool exact_only = (c.fp.flags & 1) != 0;
   if ((COUNT & K_OBJ) && (H.special & S_OBJ)) { obj_leaf<COUNT>(c, H, C, first, last, exact_only); return; }
   for (int k = first; k < last; ++k) {
     bump<COUNT>(c, C_TRI_FILTER);
     bool pass = exact_only;
     int i = k;
-    if (H.special) i = c.sv.tri_pos[k];
+    if (XP && H.special) i = c.sv.tri_pos[k];
     if (!exact_only) {
       const char *p = reinterpret_cast<const char *>(c.sv.filt + i);
       const F4 a = ld_f4(p), b = ld_f4(p + 16), d = ld_f4(p + 32);
@@ -351,7 +358,7 @@ struct alignas(8) StackEntry {
 // The kernel calls this from a WARP-UNIFORM loop (while (__any_sync(node >= 0)) if (node >= 0) step):
 // the vote re-converges the warp every iteration.  A per-lane `while (node >= 0)` loop lets lanes
 // drift out of phase and ran 2x slower on B200 (profiles/r01_variants.md).
-template <int COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
+template <int COUNT, bool XP, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   const char *np = reinterpret_cast<const char *>(c.sv.nodes) + (size_t)(unsigned)H.node * 64u;
   const W8 lo = ld_w8(np), hi = ld_w8(np + 32);   // two 32-byte loads per 64-byte record
   I4 r; r.x = (int)hi.w[4]; r.y = (int)hi.w[5]; r.z = (int)hi.w[6]; r.w = (int)hi.w[7];
@@ -363,7 +370,7 @@ template <int COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Col
   float tn0, tn1;
   bool h0 = box_test(H.rf, b0c, b0h, H.thiS, tn0);
   bool h1 = box_test(H.rf, b1c, b1h, H.thiS, tn1);
-  if (H.special == S_XPAR) { // rare (exactly axis-parallel rays in the reference tree): reproduce its NaN rejection
+  if (XP && H.special == S_XPAR) { // rare (exactly axis-parallel rays in the reference tree): reproduce its NaN rejection
     const NodeMaxX mx = c.sv.maxx[H.node - c.sv.q_base];
     const double ox = C.d(CD_O);
     h0 = h0 && !(ox == mx.c0_max_x);
@@ -371,7 +378,7 @@ template <int COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Col
   }
   const bool l0 = h0 && r.z > 0, l1 = h1 && r.w > 0;
   if (l0 || l1) {
-    leaf_test<COUNT>(c, H, C, l0 ? r.x : r.y, l1 ? r.y + r.w : r.x + r.z);
+    leaf_test<COUNT, XP>(c, H, C, l0 ? r.x : r.y, l1 ? r.y + r.w : r.x + r.z);
     if (H.found) { H.node = -1; return; }
     h0 = h0 && !l0;
     h1 = h1 && !l1;
@@ -402,7 +409,8 @@ template <int COUNT, int S> RT_HD void trav_step(const Ctx &c, Hot &H, const Col
 // host/test build: run this lane's ray to completion
 template <int COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   do {
-    while (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
+    unpark(H.node);
+    while (H.node >= 0) trav_step<COUNT, true>(c, H, C, stk);
   } while (next_tree<COUNT>(c, H, C));
 }
 
@@ -555,7 +563,7 @@ template <int S> RT_HD void add_light(const Ctx &c, const Cold<S> &C, const Mat 
 // Advance a lane whose traversal has finished until it has a new ray in flight or is idle.
 template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<S> &C) {
   const SceneView &sv = c.sv;
-  while (H.mode != M_IDLE && H.node < 0) {
+  while (H.mode != M_IDLE && H.node == -1) { // -1: no ray in flight (a parked node is <= -2)
     Mat m;
     if (H.mode == M_NEAREST) {
       if (C.i(CI_DEPTH) == 0 && c.fp.spp_grid == 1) {

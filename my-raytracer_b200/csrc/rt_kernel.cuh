@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
 
   while (true) {
     // ---- phase A: path logic (FP64, cold state) for lanes whose traversal finished -----------
-    if (H.mode != M_IDLE && H.node < 0) advance<COUNT>(c, H, C);
+    if (H.mode != M_IDLE && H.node == -1) advance<COUNT>(c, H, C);
 
     // ---- warp-level work fetch for idle lanes ----------------------------------------------
     const unsigned idle = __ballot_sync(kFullMask, H.mode == M_IDLE);
@@ -170,7 +170,13 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     // low lane counts — 10.8-17 ms instead of 7.2, profiles/r01_variants.md.)
     for (;;) {
       while (__any_sync(kFullMask, H.node >= 0)) {
-        if (H.node >= 0) trav_step<COUNT>(c, H, C, stk);
+        if (H.node >= 0) trav_step<COUNT, false>(c, H, C, stk);
+      }
+      // rays with direction.x == 0 were parked (rt_core.cuh park()): they walk the reference tree with the step
+      // that knows its NaN quirk and its primitive numbering
+      unpark(H.node);
+      while (__any_sync(kFullMask, H.node >= 0)) {
+        if (H.node >= 0) trav_step<COUNT, true>(c, H, C, stk);
       }
       // rays that finished the tree over the analytic spheres move on to the triangle tree (rt_core.cuh)
       if (!(COUNT & K_OBJ)) break;

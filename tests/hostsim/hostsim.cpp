@@ -87,7 +87,7 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
       H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0;
       begin_pixel<K_COUNT | K_OBJ>(ct, H, Cd, px, py);
       while (H.mode != M_IDLE) {
-        if (H.node >= 0) traverse<K_COUNT | K_OBJ>(ct, H, Cd, stk);
+        if (H.node != -1) traverse<K_COUNT | K_OBJ>(ct, H, Cd, stk);
         else advance<K_COUNT | K_OBJ>(ct, H, Cd);
       }
       if (cost_nodes) cost_nodes[(size_t)py * ct.fp.cam.width + px] = cnt[C_NODES];
