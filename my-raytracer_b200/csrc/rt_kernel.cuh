@@ -165,6 +165,7 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
       continue;
     }
     // ---- phase B: one traversal loop for every ray type (hot state, FP32) -------------------
+    // (Two steps per vote: 13 % slower — the warp must re-converge after every step.)
     // (Leaving the loop early to refill finished lanes was measured and is a loss: lanes of one warp then
     // work on rays of different generations, the node loads stop coalescing and the shading code runs at
     // low lane counts — 10.8-17 ms instead of 7.2, profiles/r01_variants.md.)
