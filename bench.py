@@ -340,7 +340,12 @@ def run_b200(args):
     t_fp32 = flops / (peak_tflops * 1e12)
     t_l2 = alg_bytes / (l2_bw * 1e9)
     roof = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-            "traffic": None, "kernel": "rtb::render_kernel<false>",
+            # DRAM bytes per launch of this kernel on this workload from the committed `ncu --set full` capture
+            # (profiles/r01_ncu_render_kernel_v6.md: dram__bytes_read.sum 8.09 MB + dram__bytes_write.sum 0.43 MB);
+            # only quoted for the configuration that capture was taken on
+            "traffic": 8525824 if (world == 1 and (W, H) == (1920, 1080) and args.topology == "sah") else None,
+            "traffic_unit": "bytes per launch (ncu, profiles/r01_ncu_render_kernel_v6.md)",
+            "kernel": "rtb::render_kernel<0>",
             "timed_over": "flops of one frame / ms_per_step of the timed region (kernels of successive frames overlap, "
                           "so the per-launch duration is not the divisor; flush and launch gaps are inside)",
             "kernel_ms_single_frame": max(rank_ms), "kernel_ms_per_rank": rank_ms,

@@ -52,10 +52,26 @@ struct Pending {
   int b, e, depth;
 };
 
+// Runs fn(begin, end, chunk) over [b, e) in `parts` chunks on as many threads (results are merged by the caller
+// with order-independent operations: min/max and integer sums, so the tree does not depend on the thread count).
+template <typename F> void chunked(int b, int e, int parts, F fn) {
+  if (parts <= 1) { fn(b, e, 0); return; }
+  std::vector<std::thread> pool;
+  const long long n = e - b;
+  for (int t = 0; t < parts; ++t) {
+    const int lo = b + (int)(n * t / parts), hi = b + (int)(n * (t + 1) / parts);
+    pool.emplace_back([=]() { fn(lo, hi, t); });
+  }
+  for (std::thread &t : pool) t.join();
+}
+
+constexpr int kParallelMin = 400000; // nodes at least this large are binned by several threads
+
 struct Builder {
   const float *lo, *hi;
   std::vector<float> cen; // 3 per primitive
   int *order;
+  int threads = 1;
 
   const float *plo(int p) const { return lo + 3 * (size_t)p; }
   const float *phi(int p) const { return hi + 3 * (size_t)p; }
@@ -66,12 +82,24 @@ struct Builder {
     const int n = e - b;
     if (n <= 2) return -1;
     float cl[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, ch[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    for (int i = b; i < e; ++i)
-      for (int k = 0; k < 3; ++k) {
-        const float v = c(order[i], k);
-        cl[k] = v < cl[k] ? v : cl[k];
-        ch[k] = v > ch[k] ? v : ch[k];
-      }
+    const int parts = (n >= kParallelMin) ? threads : 1;
+    {
+      std::vector<Box> part(parts);
+      chunked(b, e, parts, [&](int lo_, int hi_, int t) {
+        Box x;
+        x.reset();
+        for (int i = lo_; i < hi_; ++i) {
+          const float *cp = &cen[3 * (size_t)order[i]];
+          x.grow(cp, cp);
+        }
+        part[t] = x;
+      });
+      for (const Box &x : part)
+        for (int k = 0; k < 3; ++k) {
+          cl[k] = x.lo[k] < cl[k] ? x.lo[k] : cl[k];
+          ch[k] = x.hi[k] > ch[k] ? x.hi[k] : ch[k];
+        }
+    }
     int wide = 0;
     for (int k = 1; k < 3; ++k)
       if (ch[k] - cl[k] > ch[wide] - cl[wide]) wide = k;
@@ -131,12 +159,25 @@ struct Builder {
       Box bb[kBins];
       int cnt[kBins];
       for (int k = 0; k < kBins; ++k) bb[k].reset(), cnt[k] = 0;
-      for (int i = b; i < e; ++i) {
-        const int p = order[i];
-        int k = (int)((c(p, ax) - cl[ax]) * scale);
-        k = k < 0 ? 0 : (k >= kBins ? kBins - 1 : k);
-        bb[k].grow(plo(p), phi(p));
-        ++cnt[k];
+      {
+        struct Bins { Box bb[kBins]; int cnt[kBins]; };
+        std::vector<Bins> part(parts);
+        chunked(b, e, parts, [&](int lo_, int hi_, int t) {
+          Bins &q = part[t];
+          for (int k = 0; k < kBins; ++k) q.bb[k].reset(), q.cnt[k] = 0;
+          for (int i = lo_; i < hi_; ++i) {
+            const int p = order[i];
+            int k = (int)((c(p, ax) - cl[ax]) * scale);
+            k = k < 0 ? 0 : (k >= kBins ? kBins - 1 : k);
+            q.bb[k].grow(plo(p), phi(p));
+            ++q.cnt[k];
+          }
+        });
+        for (const Bins &q : part)
+          for (int k = 0; k < kBins; ++k) {
+            if (q.cnt[k]) bb[k].grow(q.bb[k]);
+            cnt[k] += q.cnt[k];
+          }
       }
       float ra[kBins];
       int rc[kBins];
@@ -171,9 +212,17 @@ struct Builder {
   }
 
   Box bounds(int b, int e) const {
+    const int parts = (e - b >= kParallelMin) ? threads : 1;
+    std::vector<Box> part(parts);
+    chunked(b, e, parts, [&](int lo_, int hi_, int t) {
+      Box x;
+      x.reset();
+      for (int i = lo_; i < hi_; ++i) x.grow(plo(order[i]), phi(order[i]));
+      part[t] = x;
+    });
     Box x;
     x.reset();
-    for (int i = b; i < e; ++i) x.grow(plo(order[i]), phi(order[i]));
+    for (const Box &q : part) x.grow(q);
     return x;
   }
 
@@ -220,6 +269,7 @@ void build_sah(const float *lo, const float *hi, int n, std::vector<int> &order,
   unsigned hw = std::thread::hardware_concurrency();
   if (hw == 0) hw = 1;
   if (hw > 32) hw = 32;
+  B.threads = (int)hw;
   if (n < 200000 || hw == 1) {
     nodes.reserve(2 * (size_t)n);
     B.build(nodes, 0, n, 1, depth, 0, nullptr);
