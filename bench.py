@@ -218,13 +218,15 @@ def run_b200(args):
     info = scene.info()
     cam = host.camera
     chunk = int(os.environ.get("RT_TILE_CHUNK", "0")) or None
-    # frames in flight: 4 full-width grids up to 4 GPUs; at 8 GPUs a frame is ~0.25 ms, comparable to the time of a
-    # single heavy tile, so 8 frames are kept in flight on quarter-width grids (1 CTA per SM each: four frames are
-    # resident side by side and every warp renders 4x more tiles of its frame) - profiles/r01_variants.md
-    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "8" if world >= 8 else "4"))
+    # frames in flight: 4 full-width grids on one GPU.  Split over N GPUs a frame shrinks towards the time of a
+    # single heavy tile (8 GPUs: ~0.2 ms of work per GPU), so 8 frames are kept in flight on narrower grids (2 CTAs
+    # per SM each at 2-4 GPUs, 1 at 8: frames resident side by side, every warp renders 2-4x more tiles of its
+    # frame) - profiles/r01_variants.md
+    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "8" if world >= 2 else "4"))
     dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", "0.15"))
     FLUSH = int(os.environ.get("RT_FLUSH_MB", "160")) * 1024 * 1024             # > 126 MB L2 (env: experiments only)
-    ctas = int(os.environ.get("RT_CTAS_PER_SM", "1" if world >= 8 else "0"))     # 0 = full-width grids
+    # 0 = full-width grids (one GPU); half-width at 2-4 GPUs; quarter-width at 8
+    ctas = int(os.environ.get("RT_CTAS_PER_SM", "0" if world == 1 else ("2" if world < 8 else "1")))
     pipe = rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, tile_chunk=chunk,
                                dyn_fraction=dyn_fraction, flush_bytes=FLUSH, ctas_per_sm=ctas)
     nl = pipe.nl
