@@ -329,7 +329,21 @@ def run_b200(args):
                       "mrays": rays_frame / (k2 * 1e-3) / 1e6,
                       "note": "same frame bit for bit (tests/test_gpu_parity.py); compare with latency_ms_single_frame"}
         sc2.close()
+    # ---- A/B: ordinary rays on the binary traversal tree instead of its 4-wide twin (N = 1, serial frames) ----
+    binary_nodes = None
+    if world == 1 and not args.no_ab and info.get("num_nodes_wide", 0) > 0:
+        bparams = host.params(tile=pipe.tile, flags=capi.RT_FLAG_NO_CLEAR | capi.RT_FLAG_BINARY_NODES)
+        ms3 = []
+        for i in range(8):
+            pipe.flush.fill_(1)
+            capi.check(lib.rt_render_device(scene.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
+                                            C.byref(bparams), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
+            ms3.append(scene.last_kernel_ms())
+        k3 = sum(ms3[2:]) / len(ms3[2:])
+        binary_nodes = {"kernel_ms_single_frame": k3, "mrays": rays_frame / (k3 * 1e-3) / 1e6,
+                        "note": "RT_FLAG_BINARY_NODES, same frame bit for bit; compare with latency_ms_single_frame"}
 
+    wide = tot.get("nodes4_visited", 0) > 0      # ordinary rays walked the 4-wide tree (render_kernel<K_WIDE>)
     # ---- roofline of the render kernel -------------------------------------------------------------
     peaks = measured_peaks()
     sm_max = float(peaks.get("sm_max_mhz", 1965.0))
@@ -347,7 +361,7 @@ def run_b200(args):
             # only quoted for the configuration that capture was taken on
             "traffic": 8525824 if (world == 1 and (W, H) == (1920, 1080) and args.topology == "sah") else None,
             "traffic_unit": "bytes per launch (ncu, profiles/r01_ncu_render_kernel_v6.md)",
-            "kernel": "rtb::render_kernel<0>",
+            "kernel": "rtb::render_kernel<4>" if wide else "rtb::render_kernel<0>",
             "timed_over": "flops of one frame / ms_per_step of the timed region (kernels of successive frames overlap, "
                           "so the per-launch duration is not the divisor; flush and launch gaps are inside)",
             "kernel_ms_single_frame": max(rank_ms), "kernel_ms_per_rank": rank_ms,
@@ -372,6 +386,7 @@ def run_b200(args):
                        "traversal_tree": ("reference median-split topology" if info["topology"] == 1 else
                                           "library-built SAH tree over the same triangles; reference tree kept for d.x == 0 rays"),
                        "traversal_records": info["num_nodes_traversal"],
+                       "node_width": 4 if wide else 2, "wide_records": info.get("num_nodes_wide", 0),
                        "lights": nl, "max_depth": desc.max_depth, "spp": 1,
                        "l2": "flushed before every timed frame (160 MiB fill on the frame's stream)",
                        "frames_in_flight": pipe.depth, "ctas_per_sm_per_frame": pipe.ctas_per_sm or "all",
@@ -382,6 +397,7 @@ def run_b200(args):
             "mrays_primary": tot["rays_primary"] / (ms_per_step * 1e-3) / 1e6,
             "latency_ms_single_frame": max(rank_ms),
             "other_tree": other_tree,
+            "binary_nodes": binary_nodes,
             "rays_per_frame": {k: tot[k] for k in ("rays_primary", "rays_shadow", "rays_reflect")},
             "counters": tot,
             "clocks": clocks,

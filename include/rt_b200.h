@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 3
+#define RT_B200_ABI_VERSION 4
 
 typedef enum rt_status {
   RT_OK = 0,
@@ -133,6 +133,7 @@ typedef struct rt_render_params {
 #define RT_FLAG_EXACT_ONLY   1 /* validation: bypass the FP32 triangle filter (every test in FP64) */
 #define RT_FLAG_COUNTERS     2 /* run the instrumented kernel and fill rt_counters */
 #define RT_FLAG_NO_CLEAR     4 /* keep pixels of tiles owned by other ranks untouched */
+#define RT_FLAG_BINARY_NODES 8 /* A/B: ordinary rays walk the binary traversal tree instead of its 4-wide twin */
 
 /* Output buffers; any pointer may be NULL.  All are W*H entries, index y*W + x
  * (mytracer_gpu.cu:158). */
@@ -155,6 +156,7 @@ typedef struct rt_counters {
   unsigned long long shadow_trivial; /* shadow rays (counted in rays_shadow) resolved without traversal:
                                         the light's contribution is exactly zero whatever the occlusion */
   unsigned long long shadow_occluded;   /* shadow rays that found an occluder */
+  unsigned long long nodes4_visited;    /* of nodes_visited: 128-byte four-child records (4-wide tree) */
 } rt_counters;
 
 typedef struct rt_scene_info {
@@ -167,6 +169,7 @@ typedef struct rt_scene_info {
   double flatten_ms, upload_ms;
   int topology;            /* 0: SAH traversal tree + reference tree for d.x == 0 rays; 1: reference tree only */
   int num_nodes_traversal; /* records of the tree ordinary rays walk */
+  int num_nodes_wide;      /* 128-byte four-child records of its 4-wide twin (0: none, e.g. scenes with an object tree) */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene;

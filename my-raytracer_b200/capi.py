@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "librt_b200.so")
 RT_OK = 0
 RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_BAD_SCENE, RT_ERR_LIMIT, RT_ERR_OOM = 1, 2, 3, 4, 5, 6
 RT_SPHERE, RT_PLANE = 0, 1
-RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR = 1, 2, 4
+RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR, RT_FLAG_BINARY_NODES = 1, 2, 4, 8
 RT_SCENE_REFERENCE_TOPOLOGY = 1
 
 c_int_p = C.POINTER(C.c_int)
@@ -95,7 +95,7 @@ class Counters(C.Structure):
     _fields_ = [(n, C.c_ulonglong) for n in (
         "rays_primary", "rays_shadow", "rays_reflect", "box_tests", "tri_filter", "tri_exact",
         "object_tests", "shaded_hits", "texel_fetches", "nodes_visited", "shadow_trivial",
-        "shadow_occluded")]
+        "shadow_occluded", "nodes4_visited")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -105,7 +105,8 @@ class SceneInfo(C.Structure):
     _fields_ = [("num_triangles", C.c_int), ("num_meshes", C.c_int), ("num_objects", C.c_int),
                 ("num_nodes_ref", C.c_int), ("num_nodes_flat", C.c_int), ("max_depth_bvh", C.c_int),
                 ("max_leaf_size", C.c_int), ("blob_bytes", C.c_size_t), ("flatten_ms", C.c_double),
-                ("upload_ms", C.c_double), ("topology", C.c_int), ("num_nodes_traversal", C.c_int)]
+                ("upload_ms", C.c_double), ("topology", C.c_int), ("num_nodes_traversal", C.c_int),
+                ("num_nodes_wide", C.c_int)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -187,7 +188,7 @@ def load_library(path: str | None = None):
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.rt_abi_version() != 3:
+    if lib.rt_abi_version() != 4:
         raise RuntimeError("rt_b200 ABI version mismatch")
     if path is None:
         _lib = lib

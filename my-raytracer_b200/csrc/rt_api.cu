@@ -62,6 +62,8 @@ struct rt_scene {
   int *d_list = nullptr; // supersampling pixel list
   size_t cap_list = 0;
   int grid_plain = 0, grid_count = 0;
+  int grid_wide = 0, grid_wide_count = 0; // K_WIDE kernels (scenes with a 4-wide tree and no object tree)
+  bool wide_ok = false;
   int sm_count = 0, ctas_per_sm = 0; // ctas_per_sm: 0 = every resident slot (rt_scene_set_launch_width)
   size_t extra_smem = 0;
   rt_counters counters;
@@ -108,6 +110,8 @@ int adopt_blob(rt_scene *s) {
   s->view.lin_idx = reinterpret_cast<const int32_t *>(b + h.off_lin_idx);
   s->view.obj_root = h.obj_root; s->view.num_lin = h.num_lin;
   s->view.tri_nodes = h.q_base + h.num_nodes_q;
+  s->view.num_nodes4 = h.num_nodes4;
+  s->view.nodes4 = h.num_nodes4 > 0 ? reinterpret_cast<const Node4Rec *>(b + h.off_nodes4) : nullptr;
   s->view.texels = reinterpret_cast<const float *>(b + h.off_texels);
   s->view.num_nodes = h.num_nodes; s->view.num_tris = h.num_tris;
   s->view.num_meshes = h.num_meshes; s->view.num_objects = h.num_objects;
@@ -171,11 +175,30 @@ int adopt_blob(rt_scene *s) {
   }
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, k_plain, kBlockThreads, s->extra_smem));
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_count, kBlockThreads, s->extra_smem));
+  // the 4-wide tree is walked by its own kernel variants; RT_B200_WIDE=0 (or RT_FLAG_BINARY_NODES per frame)
+  // keeps ordinary rays on the binary tree
+  s->wide_ok = h.num_nodes4 > 0 && !obj;
+  if (const char *e = std::getenv("RT_B200_WIDE")) if (std::atoi(e) == 0) s->wide_ok = false;
+  if (s->wide_ok) {
+    int occ2 = 0, occ3 = 0;
+    const void *k_w = (const void *)render_kernel<K_WIDE>, *k_wc = (const void *)render_kernel<K_WIDE | K_COUNT>;
+    if (s->extra_smem) {
+      RT_CUDA(cudaFuncSetAttribute(k_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+      RT_CUDA(cudaFuncSetAttribute(k_wc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+    }
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, k_w, kBlockThreads, s->extra_smem));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, k_wc, kBlockThreads, s->extra_smem));
+    s->grid_wide = prop.multiProcessorCount * (occ2 > 0 ? occ2 : 1);
+    s->grid_wide_count = prop.multiProcessorCount * (occ3 > 0 ? occ3 : 1);
+  }
   s->sm_count = prop.multiProcessorCount;
   s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
   s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
   {
-    const size_t threads = (size_t)(s->grid_plain > s->grid_count ? s->grid_plain : s->grid_count) * kBlockThreads;
+    int gmax = s->grid_plain > s->grid_count ? s->grid_plain : s->grid_count;
+    if (s->grid_wide > gmax) gmax = s->grid_wide;
+    if (s->grid_wide_count > gmax) gmax = s->grid_wide_count;
+    const size_t threads = (size_t)gmax * kBlockThreads;
     RT_CUDA(cudaMalloc(&s->d_scratch_d, threads * CD_NUM * sizeof(double)));
     RT_CUDA(cudaMalloc(&s->d_scratch_i, threads * CI_NUM * sizeof(int)));
   }
@@ -185,6 +208,7 @@ int adopt_blob(rt_scene *s) {
   s->info.max_depth_bvh = h.max_depth; s->info.max_leaf_size = h.max_leaf; s->info.blob_bytes = s->bytes;
   s->info.topology = h.topology;
   s->info.num_nodes_traversal = h.topology == 0 ? h.q_base : h.num_nodes;
+  s->info.num_nodes_wide = h.num_nodes4;
   std::memset(&s->counters, 0, sizeof(s->counters));
   return RT_OK;
 }
@@ -210,14 +234,15 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   if (count) RT_CUDA(cudaMemsetAsync(s->d_counters, 0, sizeof(unsigned long long) * C_COUNT, st));
 #ifdef RT_TAILPROBE
   {
-    unsigned long long init[C_COUNT] = {0, 0, ~0ull, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long init[C_COUNT] = {0, 0, ~0ull};
     RT_CUDA(cudaMemcpyAsync(s->d_counters, init, sizeof(init), cudaMemcpyHostToDevice, st));
   }
 #endif
   RT_CUDA(cudaEventRecord(s->ev0[slot], st));
   // frames in flight share the machine: with ctas_per_sm = k each launch takes k of the resident CTA slots of
   // every SM, so several persistent grids run side by side instead of queueing for each other's slots
-  int gc = s->grid_count, gp = s->grid_plain;
+  const bool wide = s->wide_ok && !(fp.flags & RT_FLAG_BINARY_NODES);
+  int gc = wide ? s->grid_wide_count : s->grid_count, gp = wide ? s->grid_wide : s->grid_plain;
   if (s->ctas_per_sm > 0) {
     const int lim = s->sm_count * s->ctas_per_sm;
     gc = gc < lim ? gc : lim;
@@ -226,9 +251,11 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   const bool obj = s->hdr.obj_root >= 0; // tree over analytic spheres: the kernel variant that can walk it
   if (count) {
     if (obj) render_kernel<K_COUNT | K_OBJ><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
+    else if (wide) render_kernel<K_COUNT | K_WIDE><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
     else render_kernel<K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
   } else {
     if (obj) render_kernel<K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
+    else if (wide) render_kernel<K_WIDE><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
     else render_kernel<0><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
   }
   RT_CUDA(cudaGetLastError());
@@ -248,6 +275,7 @@ int fetch_counters(rt_scene *s, cudaStream_t st) {
   c.nodes_visited = h[C_NODES];
   c.shadow_trivial = h[C_SHADOW_TRIVIAL];
   c.shadow_occluded = h[C_SHADOW_OCCLUDED];
+  c.nodes4_visited = h[C_NODES4];
   return RT_OK;
 }
 

@@ -84,7 +84,8 @@ enum Special : int { S_XPAR = 1, S_OBJ = 2 };
 // Kernel configuration bits (the template parameter named COUNT throughout): K_COUNT = instrumented build,
 // K_OBJ = the scene has a tree over analytic spheres.  Scenes without one run a kernel that contains none of
 // that code (its mere presence in the leaf path costs 3 % on the Office scene).
-enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2 };
+// K_WIDE = ordinary rays walk the 4-wide tree (Node4Rec, trav_step4); never combined with K_OBJ.
+enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2, K_WIDE = 4 };
 
 struct Mat {
   D3 ka, ks;
@@ -406,9 +407,88 @@ template <int COUNT, bool XP, int S> RT_HD void trav_step(const Ctx &c, Hot &H, 
   H.sp = sp;
 }
 
+// One step through the 4-wide tree (K_WIDE kernels, ordinary rays only): one 128-byte Node4Rec (four 32-byte
+// loads), four independent conservative slab tests (48 FMAs), hit leaf children intersected at once, the nearest
+// hit interior child next, the others pushed with their entry distances (culled when popped).  Half the
+// dependent load -> test -> branch chains of the binary step per ray, twice the independent work inside one.
+#ifndef RT_WIDE_SORT
+#define RT_WIDE_SORT 0
+#endif
+RT_HD int first_bit(unsigned m) {
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)m) - 1;
+#else
+  int k = 0;
+  while (!((m >> k) & 1u)) ++k;
+  return k;
+#endif
+}
+template <int COUNT, int S> RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
+  const char *np = reinterpret_cast<const char *>(c.sv.nodes4) + (size_t)(unsigned)H.node * 128u;
+  const W8 q0 = ld_w8(np), q1 = ld_w8(np + 32), q2 = ld_w8(np + 64), q3 = ld_w8(np + 96);
+  bump<COUNT>(c, C_NODES);
+  bump<COUNT>(c, C_NODES4);
+  // q0 = b0.ctr b0.half b1.ctr.xy | q1 = b1.ctr.z b1.half b2.ctr b2.half.x | q2 = b2.half.yz b3.ctr b3.half | q3 = ref[4] cnt[4]
+  const float b0c[3] = {w2f(q0.w[0]), w2f(q0.w[1]), w2f(q0.w[2])}, b0h[3] = {w2f(q0.w[3]), w2f(q0.w[4]), w2f(q0.w[5])};
+  const float b1c[3] = {w2f(q0.w[6]), w2f(q0.w[7]), w2f(q1.w[0])}, b1h[3] = {w2f(q1.w[1]), w2f(q1.w[2]), w2f(q1.w[3])};
+  const float b2c[3] = {w2f(q1.w[4]), w2f(q1.w[5]), w2f(q1.w[6])}, b2h[3] = {w2f(q1.w[7]), w2f(q2.w[0]), w2f(q2.w[1])};
+  const float b3c[3] = {w2f(q2.w[2]), w2f(q2.w[3]), w2f(q2.w[4])}, b3h[3] = {w2f(q2.w[5]), w2f(q2.w[6]), w2f(q2.w[7])};
+  const int r0 = (int)q3.w[0], r1 = (int)q3.w[1], r2 = (int)q3.w[2], r3 = (int)q3.w[3];
+  const int n0 = (int)q3.w[4], n1 = (int)q3.w[5], n2 = (int)q3.w[6], n3 = (int)q3.w[7];
+  if (COUNT & K_COUNT) bump<COUNT>(c, C_BOX, 2u + (unsigned)(r2 >= 0) + (unsigned)(r3 >= 0));
+  float t0, t1, t2, t3;
+  bool h0 = box_test(H.rf, b0c, b0h, H.thiS, t0);
+  bool h1 = box_test(H.rf, b1c, b1h, H.thiS, t1);
+  bool h2 = box_test(H.rf, b2c, b2h, H.thiS, t2);
+  bool h3 = box_test(H.rf, b3c, b3h, H.thiS, t3);
+  unsigned lm = (h0 && n0 > 0 ? 1u : 0u) | (h1 && n1 > 0 ? 2u : 0u) | (h2 && n2 > 0 ? 4u : 0u) | (h3 && n3 > 0 ? 8u : 0u);
+  if (lm) {
+    h0 = h0 && !(lm & 1u); h1 = h1 && !(lm & 2u); h2 = h2 && !(lm & 4u); h3 = h3 && !(lm & 8u);
+    // leaf children in ascending order of their triangle ranges; neighbours own adjacent ranges and are merged
+    do {
+      const int k = first_bit(lm);
+      lm &= lm - 1u;
+      int first = k == 0 ? r0 : (k == 1 ? r1 : (k == 2 ? r2 : r3));
+      int last = first + (k == 0 ? n0 : (k == 1 ? n1 : (k == 2 ? n2 : n3)));
+      if (lm & (2u << k)) { // the next child is a hit leaf as well: one loop for both
+        last += (k == 0 ? n1 : (k == 1 ? n2 : n3));
+        lm &= ~(2u << k);
+      }
+      leaf_test<COUNT, false>(c, H, C, first, last);
+      if (H.found) { H.node = -1; return; }
+    } while (lm);
+    // a nearer hit may have been found: surviving interior children are re-checked when visited / popped
+  }
+  int node, sp = H.sp;
+  const float INF = 3.0e38f;
+  const float u0 = h0 ? t0 : INF, u1 = h1 ? t1 : INF, u2 = h2 ? t2 : INF, u3 = h3 ? t3 : INF;
+  const float m = fminf(fminf(u0, u1), fminf(u2, u3));
+  if (m < INF) {
+    // nearest interior child next (first of equals); the others are pushed in child order (no branches)
+    const bool k0 = u0 == m, k1 = !k0 && u1 == m, k2 = !k0 && !k1 && u2 == m;
+    node = k0 ? r0 : (k1 ? r1 : (k2 ? r2 : r3));
+    if (h0 && !k0) { stk[sp].ref = r0; stk[sp].tn = t0; ++sp; }
+    if (h1 && !k1) { stk[sp].ref = r1; stk[sp].tn = t1; ++sp; }
+    if (h2 && !k2) { stk[sp].ref = r2; stk[sp].tn = t2; ++sp; }
+    if (h3 && (k0 || k1 || k2)) { stk[sp].ref = r3; stk[sp].tn = t3; ++sp; }
+  } else {
+    node = -1;
+    while (sp > 0) {
+      --sp;
+      const StackEntry e = stk[sp];
+      if (e.tn <= H.thiS) { node = e.ref; break; }
+    }
+  }
+  H.node = node;
+  H.sp = sp;
+}
+
 // host/test build: run this lane's ray to completion
 template <int COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   do {
+    if (COUNT & K_WIDE) {
+      while (H.node >= 0) trav_step4<COUNT>(c, H, C, stk); // ordinary rays; d.x == 0 rays are parked (node <= -2)
+    }
     unpark(H.node);
     while (H.node >= 0) trav_step<COUNT, true>(c, H, C, stk);
   } while (next_tree<COUNT>(c, H, C));

@@ -255,6 +255,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   std::vector<int> tri_id(N), tri_pos(N);
   for (int i = 0; i < N; ++i) tri_id[i] = tri_pos[i] = i;
   int q_base = 0, topology = 1;
+  std::vector<Node4Rec> wide;
   const int num_nodes_q = (int)nodes.size();
   if (!(flags & RT_SCENE_REFERENCE_TOPOLOGY) && N > 2 && !root_is_leaf) {
     std::vector<float> plo(3 * (size_t)N), phi(3 * (size_t)N);
@@ -301,6 +302,65 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
         trav[w.flat_idx] = n;
       }
       if (sah_depth > max_depth) max_depth = sah_depth;
+      // 4-wide twin of the same tree: a binary node's two children, then repeatedly the interior child with the
+      // largest surface area replaced IN PLACE by its own two children (so the children stay in the binary
+      // tree's left-to-right order and leaf ranges ascend) until there are four or none is interior.
+      // Records in DFS pre-order.  The kernel pushes at most (interior children - 1) entries per visit; if the
+      // worst root-to-leaf sum does not fit the traversal stack the wide tree is dropped (binary tree stays).
+      {
+        struct W4 { int sah_node, rec, stack_before; };
+        std::vector<W4> todo4;
+        wide.emplace_back();
+        todo4.push_back({0, 0, 0});
+        int worst_stack = 0;
+        auto area = [&](int k) {
+          const SahNode &b = sn[k];
+          const double dx = (double)b.hi[0] - b.lo[0], dy = (double)b.hi[1] - b.lo[1], dz = (double)b.hi[2] - b.lo[2];
+          return dx * dy + dy * dz + dz * dx;
+        };
+        while (!todo4.empty()) {
+          const W4 w = todo4.back();
+          todo4.pop_back();
+          int slot[4], ns = 2;
+          slot[0] = sn[w.sah_node].left; slot[1] = sn[w.sah_node].right;
+          while (ns < 4) {
+            int pick = -1;
+            double best_area = -1.0;
+            for (int k = 0; k < ns; ++k)
+              if (sn[slot[k]].count == 0 && area(slot[k]) > best_area) { best_area = area(slot[k]); pick = k; }
+            if (pick < 0) break;
+            const int l = sn[slot[pick]].left, r = sn[slot[pick]].right;
+            for (int k = ns; k > pick + 1; --k) slot[k] = slot[k - 1];
+            slot[pick] = l; slot[pick + 1] = r;
+            ++ns;
+          }
+          Node4Rec n;
+          int child_rec[4] = {-1, -1, -1, -1}, interior = 0;
+          for (int k = 0; k < 4; ++k) {
+            if (k >= ns) {
+              for (int a = 0; a < 3; ++a) n.box[k][a] = 0.0f, n.box[k][3 + a] = -1e30f;
+              n.ref[k] = -1; n.cnt[k] = 0;
+              continue;
+            }
+            const SahNode &cn = sn[slot[k]];
+            const double lo[3] = {cn.lo[0], cn.lo[1], cn.lo[2]}, hi[3] = {cn.hi[0], cn.hi[1], cn.hi[2]};
+            box_lohi(lo, hi, &n.box[k][0], &n.box[k][3]);
+            if (cn.count > 0) { n.ref[k] = cn.first; n.cnt[k] = cn.count; }
+            else {
+              child_rec[k] = (int)wide.size();
+              wide.emplace_back();
+              n.ref[k] = child_rec[k]; n.cnt[k] = 0;
+              ++interior;
+            }
+          }
+          const int stack_after = w.stack_before + (interior > 1 ? interior - 1 : 0);
+          if (stack_after > worst_stack) worst_stack = stack_after;
+          for (int k = 3; k >= 0; --k)
+            if (child_rec[k] >= 0) todo4.push_back({slot[k], child_rec[k], stack_after});
+          wide[w.rec] = n;
+        }
+        if (worst_stack > kStackMax) wide.clear();
+      }
       q_base = (int)trav.size();
       topology = 0;
       for (NodeRec &r : nodes) { // reference tree: interior child references move behind the traversal tree
@@ -470,6 +530,8 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.off_objfilt = off; off = align_up(off + objf.size() * sizeof(ObjFilter), kSectionAlign);
   h.off_obj_order = off; off = align_up(off + obj_order.size() * sizeof(int32_t), kSectionAlign);
   h.off_lin_idx = off; off = align_up(off + lin_idx.size() * sizeof(int32_t), kSectionAlign);
+  h.off_nodes4 = off;  off = align_up(off + wide.size() * sizeof(Node4Rec), kSectionAlign);
+  h.num_nodes4 = (int)wide.size();
   h.obj_root = obj_root; h.num_nodes_obj = num_nodes_obj; h.num_obj_tree = (int)obj_order.size(); h.num_lin = (int)lin_idx.size();
   h.q_base = q_base; h.num_nodes_q = num_nodes_q; h.topology = topology;
   h.root_max_x = N > 0 ? bvh->bb_max_[0].x : 0.0;
@@ -490,6 +552,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   if (num_objects > 0) std::memcpy(blob.data() + h.off_objfilt, objf.data(), objf.size() * sizeof(ObjFilter));
   if (!obj_order.empty()) std::memcpy(blob.data() + h.off_obj_order, obj_order.data(), obj_order.size() * sizeof(int32_t));
   if (!lin_idx.empty()) std::memcpy(blob.data() + h.off_lin_idx, lin_idx.data(), lin_idx.size() * sizeof(int32_t));
+  if (!wide.empty()) std::memcpy(blob.data() + h.off_nodes4, wide.data(), wide.size() * sizeof(Node4Rec));
   float *tx = reinterpret_cast<float *>(blob.data() + h.off_texels);
   for (size_t t = 0; t < num_texels; ++t) {
     const rt_vec4 &c = data->meshTexels_[t];
@@ -516,7 +579,9 @@ int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
                   h.off_tri_pos + (size_t)h.num_tris * sizeof(int32_t) <= h.off_objfilt &&
                   h.off_objfilt + (size_t)h.num_objects * sizeof(ObjFilter) <= h.off_obj_order &&
                   h.off_obj_order + (size_t)h.num_obj_tree * sizeof(int32_t) <= h.off_lin_idx &&
-                  h.off_lin_idx + (size_t)h.num_lin * sizeof(int32_t) <= h.total_bytes &&
+                  h.off_lin_idx + (size_t)h.num_lin * sizeof(int32_t) <= h.off_nodes4 &&
+                  h.num_nodes4 >= 0 && h.off_nodes4 % 32 == 0 &&
+                  h.off_nodes4 + (size_t)h.num_nodes4 * sizeof(Node4Rec) <= h.total_bytes &&
                   h.num_nodes_obj >= 0 && h.num_obj_tree >= 0 && h.num_lin >= 0 && h.num_obj_tree + h.num_lin == h.num_objects &&
                   (h.obj_root < 0 ? h.num_nodes_obj == 0 : h.obj_root == h.q_base + h.num_nodes_q) &&
                   h.q_base >= 0 && h.num_nodes_q >= 0 && (size_t)h.q_base + (size_t)h.num_nodes_q + (size_t)h.num_nodes_obj == (size_t)h.num_nodes;
@@ -538,7 +603,9 @@ SceneView view_of_blob(const unsigned char *blob) {
   v.obj_order = reinterpret_cast<const int32_t *>(blob + h.off_obj_order);
   v.lin_idx = reinterpret_cast<const int32_t *>(blob + h.off_lin_idx);
   v.obj_root = h.obj_root; v.num_lin = h.num_lin;
-  v.tri_nodes = h.q_base + h.num_nodes_q; v.pad_v = 0;
+  v.tri_nodes = h.q_base + h.num_nodes_q;
+  v.num_nodes4 = h.num_nodes4;
+  v.nodes4 = h.num_nodes4 > 0 ? reinterpret_cast<const Node4Rec *>(blob + h.off_nodes4) : nullptr;
   v.texels = reinterpret_cast<const float *>(blob + h.off_texels);
   v.tex_objs = nullptr;
   v.maxx = reinterpret_cast<const NodeMaxX *>(blob + h.off_maxx);

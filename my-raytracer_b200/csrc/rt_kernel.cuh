@@ -170,8 +170,15 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     // work on rays of different generations, the node loads stop coalescing and the shading code runs at
     // low lane counts — 10.8-17 ms instead of 7.2, profiles/r01_variants.md.)
     for (;;) {
-      while (__any_sync(kFullMask, H.node >= 0)) {
-        if (H.node >= 0) trav_step<COUNT, false>(c, H, C, stk);
+      if (COUNT & K_WIDE) {
+        // ordinary rays walk the 4-wide tree: half the dependent steps, four independent box tests in each
+        while (__any_sync(kFullMask, H.node >= 0)) {
+          if (H.node >= 0) trav_step4<COUNT>(c, H, C, stk);
+        }
+      } else {
+        while (__any_sync(kFullMask, H.node >= 0)) {
+          if (H.node >= 0) trav_step<COUNT, false>(c, H, C, stk);
+        }
       }
       // rays with direction.x == 0 were parked (rt_core.cuh park()): they walk the reference tree with the step
       // that knows its NaN quirk and its primitive numbering

@@ -4,7 +4,7 @@
 // One contiguous, 512-byte-sectioned blob (so it can be broadcast with a single NCCL call):
 //
 //   BlobHeader | NodeRec[] | TriFilter[] | TriExact[] | TriShade[] | MeshRec[] | ObjectRec[] | texels | NodeMaxX[]
-//              | tri_id[] | tri_pos[] | ObjFilter[]
+//              | tri_id[] | tri_pos[] | ObjFilter[] | obj_order[] | lin_idx[] | Node4Rec[]
 //
 // Up to three trees share the NodeRec array (rt_sah.h); the third, over the analytic spheres of
 // Raytracer::objects_ (the reference loops over them linearly per ray), is walked before the triangles: records [0, q_base) are the product's SAH traversal tree,
@@ -41,7 +41,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 8;
+constexpr uint32_t kBlobVersion = 9;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -58,6 +58,19 @@ struct alignas(16) NodeRec {
   int32_t ref0, ref1, cnt0, cnt1;
 };
 static_assert(sizeof(NodeRec) == 64, "NodeRec must be 64 bytes");
+
+// 128 B (4 x 32-byte loads): one record per node of the 4-wide traversal tree, collapsed from the binary SAH
+// tree (rt_flatten.cpp collapse_wide).  Four child boxes in the same outward-rounded centre / half-extent
+// form.  One visit = one dependent load + four independent slab tests instead of two visits of two: half the
+// dependent steps per ray and twice the instruction-level parallelism per step (the binary loop is bound by
+// its dependent chain).  Children keep the left-to-right order of the binary tree, so the
+// triangle ranges of leaf children are ascending (adjacent when the leaves are neighbours).
+struct alignas(32) Node4Rec {
+  float box[4][6];  // child k: ctr.xyz, half.xyz (an empty child has half = -1e30: never hit)
+  int32_t ref[4];   // cnt == 0: Node4Rec index of an interior child (-1: empty slot)
+  int32_t cnt[4];   // cnt  > 0: leaf child with triangle positions [ref, ref + cnt)
+};
+static_assert(sizeof(Node4Rec) == 128, "Node4Rec must be 128 bytes");
 
 struct alignas(16) TriFilter {
   float p2[3], k_bary; // vertex p2 ; 8u*max(|e1|,|e2|)   (bound on the U,V numerators, per unit rho)
@@ -135,7 +148,7 @@ struct BlobHeader {
   int32_t q_base;      // first record of the reference-topology tree (0: it IS the traversal tree)
   int32_t num_nodes_q; // its record count; num_nodes = total records of both trees
   int32_t topology;    // 0 SAH traversal tree + reference tree, 1 reference tree only
-  int32_t pad_i;
+  int32_t num_nodes4;  // records of the 4-wide traversal tree (0: none; root = record 0)
   uint64_t off_objfilt; // ObjFilter[num_objects]
   // analytic primitives: spheres go into a third tree (records [obj_base, obj_base + num_nodes_obj)) when there
   // are enough of them; everything else (planes; all objects when there is no tree) is tested linearly per ray
@@ -143,13 +156,14 @@ struct BlobHeader {
   uint64_t off_lin_idx;   // int32[num_lin]: objects tested linearly, in list order
   int32_t obj_root;       // record index of the object tree's root, -1: no object tree
   int32_t num_nodes_obj, num_obj_tree, num_lin;
-  uint64_t reserved[1];
+  uint64_t off_nodes4;    // Node4Rec[num_nodes4]
 };
 static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
 
 // Pointers into a resident blob (device pointers in the kernel, host pointers in the test build).
 struct SceneView {
   const NodeRec *nodes;
+  const Node4Rec *nodes4;   // 4-wide twin of the traversal tree [0, q_base), or nullptr
   const TriFilter *filt;
   const TriExact *exact;
   const TriShade *shade;
@@ -165,7 +179,7 @@ struct SceneView {
   const int32_t *lin_idx;   // objects tested linearly at ray start
   int32_t obj_root, num_lin;
   int32_t tri_nodes;        // records of the triangle trees (0: the scene has no triangles)
-  int32_t pad_v;
+  int32_t num_nodes4;       // records of the 4-wide tree (0: none)
   double root_max_x;
   int32_t num_nodes, num_tris, num_meshes, num_objects;
   float box_extent;
@@ -200,7 +214,7 @@ struct FrameOut {
 // indices into the counters array (RT_FLAG_COUNTERS build)
 enum Counter {
   C_RAY_PRIMARY = 0, C_RAY_SHADOW, C_RAY_REFLECT, C_BOX, C_TRI_FILTER, C_TRI_EXACT, C_OBJECT,
-  C_SHADED, C_TEXEL, C_NODES, C_SHADOW_TRIVIAL, C_SHADOW_OCCLUDED, C_COUNT
+  C_SHADED, C_TEXEL, C_NODES, C_SHADOW_TRIVIAL, C_SHADOW_OCCLUDED, C_NODES4, C_COUNT
 };
 
 } // namespace rtb

@@ -85,6 +85,34 @@ def test_frame_does_not_depend_on_the_tree(rt, lib, gpu, name, kw):
         assert a["counters"]["nodes_visited"] < b["counters"]["nodes_visited"]
 
 
+@pytest.mark.parametrize("name,kw", [
+    ("office", dict(width=640, height=360)),
+    ("scatter", dict(width=256, height=144, n_objects=300)),      # d.x == 0 rays stay on the reference tree
+    ("textured", dict(width=256, height=144, tex_size=256, slices=64, stacks=32)),
+    ("rings", dict(width=200, height=150)),
+])
+def test_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, gpu, name, kw):
+    """The 4-wide twin of the traversal tree (render_kernel<K_WIDE>, default) against the binary tree it is
+    collapsed from (RT_FLAG_BINARY_NODES), plain and instrumented kernels: bit-identical ids, distances, FP64
+    pixels; the wide walk needs fewer node visits; and the FP32 filter stays a pure filter on it."""
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    dev = rt.DeviceScene(host)
+    assert dev.info()["num_nodes_wide"] > 0
+    args = (host.camera, host.lights_pos, host.lights_color)
+    wide = dev.render(*args, host.params())
+    binary = dev.render(*args, host.params(flags=gpu.RT_FLAG_BINARY_NODES))
+    wide_c = dev.render(*args, host.params(flags=gpu.RT_FLAG_COUNTERS))
+    binary_c = dev.render(*args, host.params(flags=gpu.RT_FLAG_COUNTERS | gpu.RT_FLAG_BINARY_NODES))
+    exact = dev.render(*args, host.params(flags=gpu.RT_FLAG_EXACT_ONLY))
+    for other in (binary, wide_c, binary_c, exact):
+        for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+            assert np.array_equal(wide[k], other[k]), k
+    assert wide_c["counters"]["nodes4_visited"] > 0 and binary_c["counters"]["nodes4_visited"] == 0
+    assert wide_c["counters"]["nodes_visited"] < 0.75 * binary_c["counters"]["nodes_visited"]
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
+        assert wide_c["counters"][k] == binary_c["counters"][k], k
+
+
 def test_supersampling_grid(rt, lib, gpu):
     g = np.load(os.path.join(GOLDEN, "scene_mixed_small_spp2.npz"))
     host = rt.HostScene(rt.scenes.mixed_small(width=64, height=48), lib)

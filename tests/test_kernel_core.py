@@ -239,6 +239,28 @@ def test_frame_does_not_depend_on_the_tree(rt, lib, sim, scene, kw):
         assert b["counters"]["object_tests"] < 0.5 * a["counters"]["object_tests"]
 
 
+@pytest.mark.parametrize("scene,kw", [("office", dict(width=128, height=72)),
+                                      ("scatter", dict(width=81, height=61, n_objects=40)),
+                                      ("rings", dict(width=70, height=50, nu=48, nv=16)),
+                                      ("textured", dict(width=96, height=54, tex_size=64, slices=24, stacks=12))])
+def test_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, sim, scene, kw):
+    """The 4-wide twin of the traversal tree (Node4Rec, trav_step4) against the binary tree it is collapsed from
+    (RT_FLAG_BINARY_NODES): bit-identical ids, distances and FP64 pixels, fewer node visits; and the FP32 filter
+    stays a pure filter on the wide tree (RT_FLAG_EXACT_ONLY)."""
+    host = rt.HostScene(rt.scenes.REGISTRY[scene](**kw), lib)
+    blob = sim.flatten(host)
+    wide = sim.render(host, blob)
+    binary = sim.render(host, blob, flags=rt.capi.RT_FLAG_BINARY_NODES)
+    exact = sim.render(host, blob, flags=rt.capi.RT_FLAG_EXACT_ONLY)
+    assert wide["counters"]["nodes4_visited"] > 0 and binary["counters"]["nodes4_visited"] == 0
+    for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+        assert np.array_equal(wide[k], binary[k]), k
+        assert np.array_equal(wide[k], exact[k]), k
+    assert wide["counters"]["nodes_visited"] < 0.75 * binary["counters"]["nodes_visited"]
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
+        assert wide["counters"][k] == binary["counters"][k], k
+
+
 def test_object_tree_keeps_list_order_semantics(rt, lib, sim, orc, oracle_kind):
     """Spheres go into their own tree when there are >= 8 of them; the reference loops over objects_ in list order
     with a strict '<'.  Duplicated spheres (equal t: the lower index must win), a sphere around the camera (ray

@@ -1,5 +1,6 @@
 """Times kernel variants (my-raytracer_b200/variants/*.so) on Office 1080p (or RT_SCENE=<name>) and checks each against the
-first one bit for bit.  Usage: python tools/gpu_variants.py [names...]"""
+first one bit for bit.  Usage: python tools/gpu_variants.py [names...]; a name may carry render flags,
+e.g. wide:8 = variants/wide.so with RT_FLAG_BINARY_NODES; the name "default" is the in-tree library."""
 import os, subprocess, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CHILD = r'''
@@ -15,15 +16,19 @@ desc = rt.scenes.REGISTRY[os.environ.get("RT_SCENE", "office")]()
 host = rt.HostScene(desc, lib)
 dev = rt.DeviceScene(host)
 ms = []
+FL = int(os.environ.get("RT_VARIANT_FLAGS", "0"))
 for i in range(12):
-    out = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(), want=("rgba8", "hit_id", "hit_t"))
+    out = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(flags=FL), want=("rgba8", "hit_id", "hit_t"))
     ms.append(dev.last_kernel_ms())
 h = hashlib.sha1(out["rgba8"].tobytes() + out["hit_id"].tobytes() + out["hit_t"].tobytes()).hexdigest()
-c = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(flags=capi.RT_FLAG_COUNTERS), want=("rgba8",))["counters"]
+c = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(flags=capi.RT_FLAG_COUNTERS | FL), want=("rgba8",))["counters"]
 print(json.dumps(dict(ms_min=min(ms[2:]), ms_med=sorted(ms[2:])[5], sha=h, nodes=c["nodes_visited"], filt=c["tri_filter"], exact=c["tri_exact"])))
 ''' % ROOT
 names = sys.argv[1:] or sorted(f[:-3] for f in os.listdir(os.path.join(ROOT, "my-raytracer_b200", "variants")) if f.endswith(".so"))
 for n in names:
-    env = dict(os.environ, RT_B200_LIB=os.path.join(ROOT, "my-raytracer_b200", "variants", n + ".so"))
+    base, _, fl = n.partition(":")
+    env = dict(os.environ, RT_VARIANT_FLAGS=fl or "0")
+    if base != "default":
+        env["RT_B200_LIB"] = os.path.join(ROOT, "my-raytracer_b200", "variants", base + ".so")
     r = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True)
     print(n, r.stdout.strip() or r.stderr[-600:], flush=True)
