@@ -359,7 +359,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
             if (child_rec[k] >= 0) todo4.push_back({slot[k], child_rec[k], stack_after});
           wide[w.rec] = n;
         }
-        if (worst_stack > kStackMax) wide.clear();
+        if (worst_stack > kStackMax || wide.size() >= ((size_t)1 << 27)) wide.clear(); // (record << 4 | mask) must fit an int
       }
       q_base = (int)trav.size();
       topology = 0;

@@ -15,6 +15,9 @@
 
 namespace rtb {
 
+#ifndef RT_BOX_FOLD
+#define RT_BOX_FOLD 1
+#endif
 // Per-ray FP32 traversal constants.
 struct RayF {
   float ox, oy, oz;    // origin rounded to FP32            (triangle filter)
@@ -45,7 +48,14 @@ RT_HD void rayf_setup(RayF &r, const D3 &o, const D3 &d, float E) {
   //   u|p -+ h|i|| <= u(|o| + E)|i| ;  the outer FMA rounds relative to its result.
   // Per-axis bound s = 6u(|o| + E)|i| (+ FLT_MIN), a spatial slack of 6u(|o| + E): it stays on its own
   // axis, so a ray parallel to one slab (|i| = 1e20) keeps full culling on the other two.
+  // The relative errors — i against 1/d (1.5u) and the outer FMA (u) — are relative to a slab distance of at most
+  // (|o| + E)|i|, so they are absolute errors of at most 2.5u(|o| + E)|i| as well: with RT_BOX_FOLD they are folded
+  // into s (7u needed in total, 8u used: a larger slack makes shadow rays re-test the surface they start on) and the box test needs no relative slack on the far distance (one FMA per box).
+#if RT_BOX_FOLD
+  const float k = 8.0f * kU32;
+#else
   const float k = 6.0f * kU32; // 4u from the analysis above + margin
+#endif
   const float sx = k * (fabsf(r.ox) + E) * r.ax + FLT_MIN;
   const float sy = k * (fabsf(r.oy) + E) * r.ay + FLT_MIN;
   const float sz = k * (fabsf(r.oz) + E) * r.az + FLT_MIN;
@@ -65,7 +75,8 @@ RT_HD float this_of(float thi) { return fminf(thi * (1.0f + 16.0f * kU32), FLT_M
 // mybvh.cpp:99-135 / intersectAABB_device mytracer_gpu.cu:548-596).  Twelve FMAs, no divides and
 // no selection by ray sign:
 //     t_near = c*i + (n - h|i|),   t_far = c*i + (f + h|i|)        per axis
-// hit iff max(tn, 0) <= min(tf*kFarSlack + FLT_MIN, thiS) with tn = max3(t_near), tf = min3(t_far).
+// hit iff max(tn, 0) <= min(tf, thiS) with tn = max3(t_near), tf = min3(t_far) (every rounding error, absolute
+// and relative, is inside the per-axis slack s of rayf_setup; without RT_BOX_FOLD: tf*kFarSlack + FLT_MIN).
 // tf < 0 (box behind the ray): tf*slack stays negative < max(tn, 0): rejected.
 // tn (unclamped) orders the two children and is what the stack keeps.
 RT_HD bool box_test(const RayF &r, const float *c, const float *h, float thiS, float &tn) {
@@ -77,7 +88,11 @@ RT_HD bool box_test(const RayF &r, const float *c, const float *h, float thiS, f
   const float tfz = fmaf(c[2], r.iz, fmaf(h[2], r.az, r.fz));
   tn = fmax3(tnx, tny, tnz);
   const float tf = fmin3(tfx, tfy, tfz);
+#if RT_BOX_FOLD
+  return fmaxf(tn, 0.0f) <= fminf(tf, thiS);
+#else
   return fmaxf(tn, 0.0f) <= fminf(fmaf(tf, kFarSlack, FLT_MIN), thiS);
+#endif
 }
 
 // FP32 conservative triangle filter.  thi = upper bound (FP32, rounded up) on the ray
@@ -124,10 +139,12 @@ RT_HD bool tri_exact(const D3 &o, const D3 &d, const D3 &p0, const D3 &p1, const
   const D3 c4 = sub(o, p2);
   const double S = det3(c1, c2, c3);
   if (fabs(S) < 1e-10) return false;
-  const double alpha = ddiv(det3(c4, c2, c3), S);
-  const double beta = ddiv(det3(c1, c4, c3), S);
+  // three quotients by the same determinant: one shared reciprocal (rt_math.cuh div3), bit-identical to three '/'
+  const D3 q = div3(mk(det3(c4, c2, c3), det3(c1, c4, c3), det3(c1, c2, c4)), S);
+  const double alpha = q.x;
+  const double beta = q.y;
   const double gamma = dsub(dsub(1.0, alpha), beta);
-  const double t = ddiv(det3(c1, c2, c4), S);
+  const double t = q.z;
   if (t <= 1e-5) return false;
   const bool inside = (0.0 <= alpha && alpha <= 1.0) && (0.0 <= beta && beta <= 1.0) &&
                       (0.0 <= gamma && gamma <= 1.0);
@@ -179,8 +196,9 @@ RT_HD bool sphere_exact(const D3 &o, const D3 &d, const D3 &center, double radiu
   const double disc = dsub(dmul(b, b), dmul(dmul(4.0, a), c));
   if (disc < 0.0) return false;
   const double sq = dsqrt(disc);
-  const double t1 = ddiv(dsub(-b, sq), dmul(2.0, a));
-  const double t2 = ddiv(dadd(-b, sq), dmul(2.0, a));
+  const D3 q = div3(mk(dsub(-b, sq), dadd(-b, sq), 1.0), dmul(2.0, a)); // both roots: one shared reciprocal
+  const double t1 = q.x;
+  const double t2 = q.y;
   double t = t1;
   if (!(t > 1e-5)) t = t2;
   if (!(t > 1e-5)) return false;
