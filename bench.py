@@ -34,7 +34,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOAD = "office_34k_1920x1080_1spp"
-NCU_TRAFFIC_BYTES = 8016384 + 376832   # render_kernel<4>, Office 1080p: dram read + write per launch (ncu --set full)
+NCU_TRAFFIC_BYTES = 8022528 + 444160   # render_kernel<4>, Office 1080p: dram read + write per launch (ncu --set full, profiles/r01_ncu_render_kernel_v7.md)
 METRIC = "Mrays/s (Office 1920x1080 1spp; rays = primary + shadow + reflection as the CPU path casts them)"
 
 
