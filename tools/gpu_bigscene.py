@@ -49,6 +49,13 @@ for i in range(4):
     r = dev.render(host.camera, host.lights_pos, host.lights_color, p, want=("rgba8",))
     ms.append(dev.last_kernel_ms())
 first = r["rgba8"]
+if out["info"].get("num_nodes_wide", 0) > 0:   # A/B: the same frame on the binary records of the traversal tree
+    msb = []
+    for i in range(3):
+        rb = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(spp_grid=spp, flags=capi.RT_FLAG_BINARY_NODES), want=("rgba8",))
+        msb.append(dev.last_kernel_ms())
+    assert np.array_equal(rb["rgba8"], first)
+    out["kernel_ms_binary_nodes"] = min(msb[1:])
 c = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(spp_grid=spp, flags=capi.RT_FLAG_COUNTERS), want=("rgba8",))
 cnt = c["counters"]
 assert np.array_equal(c["rgba8"], first)                               # determinism / instrumented == plain
@@ -58,7 +65,7 @@ out.update(kernel_ms=min(ms[1:]), kernel_ms_all=ms, counters=cnt, mrays_per_s=ra
            flops=24 * cnt["box_tests"] + 48 * cnt["tri_filter"] + 140 * cnt["shaded_hits"])
 out["alg_GBps"] = out["alg_bytes"] / (out["kernel_ms"] * 1e-3) / 1e9
 out["fp32_TFLOPs"] = out["flops"] / (out["kernel_ms"] * 1e-3) / 1e12
-print(json.dumps({k: out[k] for k in ("kernel_ms", "kernel_ms_all", "mrays_per_s", "alg_GBps", "fp32_TFLOPs", "counters")}), flush=True)
+print(json.dumps({k: out.get(k) for k in ("kernel_ms", "kernel_ms_binary_nodes", "kernel_ms_all", "mrays_per_s", "alg_GBps", "fp32_TFLOPs", "counters")}), flush=True)
 # properties at full scene size on a reduced frame: filter == exact-only, ids/t against the oracle on sampled rows
 small = rt.scenes.scatter(width=480, height=270, n_objects=n_obj)
 hs = host
