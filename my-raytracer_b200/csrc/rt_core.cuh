@@ -410,7 +410,7 @@ template <int COUNT, bool XP, int S> RT_HD void trav_step(const Ctx &c, Hot &H, 
 }
 
 // One step through the 4-wide tree (K_WIDE kernels, ordinary rays only): one 128-byte Node4Rec (four 32-byte
-// loads), four independent conservative slab tests (48 FMAs), hit leaf children intersected at once, the nearest
+// loads), four independent conservative slab tests (48 FMAs as 24 FFMA2, box_pair), hit leaf children intersected at once, the nearest
 // hit interior child next, the others pushed with their entry distances (culled when popped).  Half the
 // dependent load -> test -> branch chains of the binary step per ray, twice the independent work inside one.
 #ifndef RT_DEFER_LEAF
@@ -472,19 +472,17 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   const W8 q0 = ld_w8(np), q1 = ld_w8(np + 32), q2 = ld_w8(np + 64), q3 = ld_w8(np + 96);
   bump<COUNT>(c, C_NODES);
   bump<COUNT>(c, C_NODES4);
-  // q0 = b0.ctr b0.half b1.ctr.xy | q1 = b1.ctr.z b1.half b2.ctr b2.half.x | q2 = b2.half.yz b3.ctr b3.half | q3 = ref[4] cnt[4]
-  const float b0c[3] = {w2f(q0.w[0]), w2f(q0.w[1]), w2f(q0.w[2])}, b0h[3] = {w2f(q0.w[3]), w2f(q0.w[4]), w2f(q0.w[5])};
-  const float b1c[3] = {w2f(q0.w[6]), w2f(q0.w[7]), w2f(q1.w[0])}, b1h[3] = {w2f(q1.w[1]), w2f(q1.w[2]), w2f(q1.w[3])};
-  const float b2c[3] = {w2f(q1.w[4]), w2f(q1.w[5]), w2f(q1.w[6])}, b2h[3] = {w2f(q1.w[7]), w2f(q2.w[0]), w2f(q2.w[1])};
-  const float b3c[3] = {w2f(q2.w[2]), w2f(q2.w[3]), w2f(q2.w[4])}, b3h[3] = {w2f(q2.w[5]), w2f(q2.w[6]), w2f(q2.w[7])};
+  // q0 q1 q2 = the two child pairs, 12 words each (rt_types.h Node4Rec) | q3 = ref[4] cnt[4]
+  float w[24];
+  RT_UNROLL
+  for (int k = 0; k < 8; ++k) { w[k] = w2f(q0.w[k]); w[8 + k] = w2f(q1.w[k]); w[16 + k] = w2f(q2.w[k]); }
   const int r0 = (int)q3.w[0], r1 = (int)q3.w[1], r2 = (int)q3.w[2], r3 = (int)q3.w[3];
   const int n0 = (int)q3.w[4], n1 = (int)q3.w[5], n2 = (int)q3.w[6], n3 = (int)q3.w[7];
   if (COUNT & K_COUNT) bump<COUNT>(c, C_BOX, 2u + (unsigned)(r2 >= 0) + (unsigned)(r3 >= 0));
   float t0, t1, t2, t3;
-  bool h0 = box_test(H.rf, b0c, b0h, H.thiS, t0);
-  bool h1 = box_test(H.rf, b1c, b1h, H.thiS, t1);
-  bool h2 = box_test(H.rf, b2c, b2h, H.thiS, t2);
-  bool h3 = box_test(H.rf, b3c, b3h, H.thiS, t3);
+  bool h0, h1, h2, h3;
+  box_pair(H.rf, w, H.thiS, t0, t1, h0, h1);
+  box_pair(H.rf, w + 12, H.thiS, t2, t3, h2, h3);
   unsigned lm = (h0 && n0 > 0 ? 1u : 0u) | (h1 && n1 > 0 ? 2u : 0u) | (h2 && n2 > 0 ? 4u : 0u) | (h3 && n3 > 0 ? 8u : 0u);
   if (lm) {
     h0 = h0 && !(lm & 1u); h1 = h1 && !(lm & 2u); h2 = h2 && !(lm & 4u); h3 = h3 && !(lm & 8u);

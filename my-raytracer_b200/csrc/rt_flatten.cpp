@@ -337,14 +337,18 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
           Node4Rec n;
           int child_rec[4] = {-1, -1, -1, -1}, interior = 0;
           for (int k = 0; k < 4; ++k) {
+            float ctr[3] = {0.0f, 0.0f, 0.0f}, half[3] = {-1e30f, -1e30f, -1e30f};
+            if (k < ns) {
+              const SahNode &cb = sn[slot[k]];
+              const double lo[3] = {cb.lo[0], cb.lo[1], cb.lo[2]}, hi[3] = {cb.hi[0], cb.hi[1], cb.hi[2]};
+              box_lohi(lo, hi, ctr, half);
+            }
+            for (int a = 0; a < 3; ++a) n.box[k >> 1][a][k & 1] = ctr[a], n.box[k >> 1][3 + a][k & 1] = half[a];
             if (k >= ns) {
-              for (int a = 0; a < 3; ++a) n.box[k][a] = 0.0f, n.box[k][3 + a] = -1e30f;
               n.ref[k] = -1; n.cnt[k] = 0;
               continue;
             }
             const SahNode &cn = sn[slot[k]];
-            const double lo[3] = {cn.lo[0], cn.lo[1], cn.lo[2]}, hi[3] = {cn.hi[0], cn.hi[1], cn.hi[2]};
-            box_lohi(lo, hi, &n.box[k][0], &n.box[k][3]);
             if (cn.count > 0) { n.ref[k] = cn.first; n.cnt[k] = cn.count; }
             else {
               child_rec[k] = (int)wide.size();

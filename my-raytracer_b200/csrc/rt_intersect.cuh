@@ -95,6 +95,44 @@ RT_HD bool box_test(const RayF &r, const float *c, const float *h, float thiS, f
 #endif
 }
 
+// Two child boxes of a Node4Rec pair at once.  w = the pair's 12 words: cx(a) cx(b) cy(a) cy(b) cz(a) cz(b)
+// hx(a) hx(b) hy(a) hy(b) hz(a) hz(b) (rt_types.h).  On sm_100 the twelve FMAs of a box pair with its sibling's: FFMA2
+// (fma.rn.f32x2) multiplies a register PAIR by a broadcast scalar and adds a broadcast scalar or a pair, so the
+// pair layout of the record (a 256-bit load leaves (a, b) in an aligned register pair) turns 24 FFMA into 12
+// FFMA2 with no extra registers for the ray constants.  Each half is an IEEE fma: bit-identical to box_test().
+#ifndef RT_FFMA2
+#define RT_FFMA2 1
+#endif
+#if defined(__CUDA_ARCH__) && RT_FFMA2 && RT_BOX_FOLD
+// (r0, r1) = (a0, a1) * s + (c0, c1)
+__device__ __forceinline__ void fma2_pair(float &r0, float &r1, float a0, float a1, float s, float c0, float c1) {
+  asm("{ .reg .b64 ra, rs, rc, rd; mov.b64 ra, {%2,%3}; mov.b64 rs, {%4,%4}; mov.b64 rc, {%5,%6};"
+      " fma.rn.f32x2 rd, ra, rs, rc; mov.b64 {%0,%1}, rd; }"
+      : "=f"(r0), "=f"(r1) : "f"(a0), "f"(a1), "f"(s), "f"(c0), "f"(c1));
+}
+#endif
+RT_HD void box_pair(const RayF &r, const float *w, float thiS, float &tnA, float &tnB, bool &hA, bool &hB) {
+#if defined(__CUDA_ARCH__) && RT_FFMA2 && RT_BOX_FOLD
+  float nA, nB, fA, fB;
+  float tnxA, tnxB, tnyA, tnyB, tnzA, tnzB, tfxA, tfxB, tfyA, tfyB, tfzA, tfzB;
+  fma2_pair(nA, nB, w[6], w[7], -r.ax, r.nx, r.nx);  fma2_pair(tnxA, tnxB, w[0], w[1], r.ix, nA, nB);
+  fma2_pair(fA, fB, w[6], w[7], r.ax, r.fx, r.fx);   fma2_pair(tfxA, tfxB, w[0], w[1], r.ix, fA, fB);
+  fma2_pair(nA, nB, w[8], w[9], -r.ay, r.ny, r.ny);  fma2_pair(tnyA, tnyB, w[2], w[3], r.iy, nA, nB);
+  fma2_pair(fA, fB, w[8], w[9], r.ay, r.fy, r.fy);   fma2_pair(tfyA, tfyB, w[2], w[3], r.iy, fA, fB);
+  fma2_pair(nA, nB, w[10], w[11], -r.az, r.nz, r.nz); fma2_pair(tnzA, tnzB, w[4], w[5], r.iz, nA, nB);
+  fma2_pair(fA, fB, w[10], w[11], r.az, r.fz, r.fz);  fma2_pair(tfzA, tfzB, w[4], w[5], r.iz, fA, fB);
+  tnA = fmax3(tnxA, tnyA, tnzA);
+  tnB = fmax3(tnxB, tnyB, tnzB);
+  hA = fmaxf(tnA, 0.0f) <= fminf(fmin3(tfxA, tfyA, tfzA), thiS);
+  hB = fmaxf(tnB, 0.0f) <= fminf(fmin3(tfxB, tfyB, tfzB), thiS);
+#else
+  const float cA[3] = {w[0], w[2], w[4]}, hfA[3] = {w[6], w[8], w[10]};
+  const float cB[3] = {w[1], w[3], w[5]}, hfB[3] = {w[7], w[9], w[11]};
+  hA = box_test(r, cA, hfA, thiS, tnA);
+  hB = box_test(r, cB, hfB, thiS, tnB);
+#endif
+}
+
 // FP32 conservative triangle filter.  thi = upper bound (FP32, rounded up) on the ray
 // parameters still of interest.  Returns false only if the exact test certainly rejects
 // the triangle or certainly yields t > thi.

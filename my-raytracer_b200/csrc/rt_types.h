@@ -41,7 +41,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 9;
+constexpr uint32_t kBlobVersion = 10;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -65,8 +65,12 @@ static_assert(sizeof(NodeRec) == 64, "NodeRec must be 64 bytes");
 // dependent steps per ray and twice the instruction-level parallelism per step (the binary loop is bound by
 // its dependent chain).  Children keep the left-to-right order of the binary tree, so the
 // triangle ranges of leaf children are ascending (adjacent when the leaves are neighbours).
+// Children are stored as two PAIRS (0,1) and (2,3) with the two boxes of a pair interleaved word by word, so that a
+// 256-bit load leaves (child a, child b) of every coordinate in an aligned register pair: the operand form of the
+// packed FP32 FMA of sm_100 (FFMA2, rt_intersect.cuh box_pair).
 struct alignas(32) Node4Rec {
-  float box[4][6];  // child k: ctr.xyz, half.xyz (an empty child has half = -1e30: never hit)
+  float box[2][6][2]; // [pair][ctr.x ctr.y ctr.z half.x half.y half.z][child a, child b]; child k = 2*pair + (a: 0, b: 1)
+                      // (an empty child has half = -1e30: never hit)
   int32_t ref[4];   // cnt == 0: Node4Rec index of an interior child (-1: empty slot)
   int32_t cnt[4];   // cnt  > 0: leaf child with triangle positions [ref, ref + cnt)
 };
