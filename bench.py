@@ -34,7 +34,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOAD = "office_34k_1920x1080_1spp"
-NCU_TRAFFIC_BYTES = 8022528 + 444160   # render_kernel<4>, Office 1080p: dram read + write per launch (ncu --set full, profiles/r01_ncu_render_kernel_v7.md)
+NCU_TRAFFIC_BYTES = 8006656 + 541440   # render_kernel<4>, Office 1080p: dram read + write per launch (ncu --set full, profiles/r01_ncu_render_kernel_v8.md)
 METRIC = "Mrays/s (Office 1920x1080 1spp; rays = primary + shadow + reflection as the CPU path casts them)"
 
 
@@ -358,10 +358,10 @@ def run_b200(args):
     t_l2 = alg_bytes / (l2_bw * 1e9)
     roof = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
             # DRAM bytes per launch of this kernel on this workload from the committed `ncu --set full` capture
-            # (profiles/r01_ncu_render_kernel_v7.md: dram__bytes_read.sum + dram__bytes_write.sum); only quoted for
+            # (profiles/r01_ncu_render_kernel_v8.md: dram__bytes_read.sum + dram__bytes_write.sum); only quoted for
             # the configuration that capture was taken on
             "traffic": NCU_TRAFFIC_BYTES if (world == 1 and (W, H) == (1920, 1080) and args.topology == "sah" and wide) else None,
-            "traffic_unit": "bytes per launch (ncu, profiles/r01_ncu_render_kernel_v7.md)",
+            "traffic_unit": "bytes per launch (ncu, profiles/r01_ncu_render_kernel_v8.md)",
             "kernel": "rtb::render_kernel<4>" if wide else "rtb::render_kernel<0>",
             "timed_over": "flops of one frame / ms_per_step of the timed region (kernels of successive frames overlap, "
                           "so the per-launch duration is not the divisor; flush and launch gaps are inside)",
