@@ -141,6 +141,9 @@ int sim_tri_exact(const double *p0, const double *p1, const double *p2, const do
   return hit ? 1 : 0;
 }
 
+// the specular power function of the shading path (rt_math.cuh pow_specular)
+double sim_pow_specular(double x, double y) { return rtb::pow_specular(x, y); }
+
 // conservative FP32 sphere pre-filter, operands rounded exactly like the flattener does
 int sim_sphere_filter(const double *center, double radius, const double *o, const double *d, double thi) {
   using namespace rtb;

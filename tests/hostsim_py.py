@@ -83,6 +83,13 @@ def tri_exact(p0, p1, p2, o, d):
     return bool(hit), out
 
 
+def pow_specular(x, y):
+    L = lib()
+    L.sim_pow_specular.restype = C.c_double
+    L.sim_pow_specular.argtypes = [C.c_double, C.c_double]
+    return L.sim_pow_specular(float(x), float(y))
+
+
 def sphere_filter(center, radius, o, d, thi):
     L = lib()
     L.sim_sphere_filter.argtypes = [_dp, C.c_double, _dp, _dp, C.c_double]

@@ -101,8 +101,9 @@ def _blob_sections(blob):
     offs = struct.unpack_from("<7Q", blob, 56)
     off_maxx, = struct.unpack_from("<Q", blob, 128)
     off_tri_id, off_tri_pos = struct.unpack_from("<2Q", blob, 144)
-    q_base, num_nodes_q, topology = struct.unpack_from("<3i", blob, 160)
-    return dict(magic=magic, version=ver, total=total, num_nodes=ints[0], num_tris=ints[1], num_meshes=ints[2],
+    q_base, num_nodes_q, topology, num_nodes4 = struct.unpack_from("<4i", blob, 160)
+    off_nodes4, = struct.unpack_from("<Q", blob, 216)
+    return dict(num_nodes4=num_nodes4, off_nodes4=off_nodes4, magic=magic, version=ver, total=total, num_nodes=ints[0], num_tris=ints[1], num_meshes=ints[2],
                 num_objects=ints[3], root_is_leaf=ints[4], max_depth=ints[5], max_leaf=ints[6], num_nodes_ref=ints[7],
                 num_texels=ntex, offs=offs, off_maxx=off_maxx, off_tri_id=off_tri_id, off_tri_pos=off_tri_pos,
                 q_base=q_base, num_nodes_q=num_nodes_q, topology=topology)
@@ -209,6 +210,59 @@ def test_flatten_builds_its_own_traversal_tree(rt, lib, sim):
     sys.setrecursionlimit(10000)
     assert walk(0) == (0, N) and (covered == 1).all()
     assert h["max_depth"] <= 64
+
+
+def test_wide_tree_structure(rt, lib, sim):
+    """The 4-wide twin of the traversal tree (Node4Rec, 128 B): children stored as two word-interleaved pairs; every
+    triangle position lies in exactly one leaf; a child's box contains the FP64 vertices of everything below it; the
+    children of a node own ascending, gap-free position ranges (so neighbouring leaves can be tested as one loop);
+    empty slots can never be hit; and the worst-case stack need (interior children - 1 per level) fits the kernel's
+    64-entry stack."""
+    host = rt.HostScene(rt.scenes.office(width=16, height=9), lib)
+    blob = sim.flatten(host)
+    h = _blob_sections(blob)
+    N = 34000
+    assert h["version"] == 10 and h["num_nodes4"] > 0 and h["off_nodes4"] % 32 == 0
+    assert h["off_nodes4"] + 128 * h["num_nodes4"] <= h["total"]
+    assert h["num_nodes4"] < 0.6 * h["q_base"]                       # at least ~2 binary records per wide record
+    rec = np.frombuffer(blob, np.float32, h["num_nodes4"] * 32, h["off_nodes4"]).reshape(-1, 32)
+    box = rec[:, :24].reshape(-1, 2, 6, 2).astype(np.float64)         # [record][pair][cx cy cz hx hy hz][child a, b]
+    ref = rec[:, 24:28].view(np.int32)
+    cnt = rec[:, 28:32].view(np.int32)
+    exact = np.frombuffer(blob, np.float64, N * 10, h["offs"][2]).reshape(N, 10)
+    verts = exact[:, :9].reshape(N, 3, 3)
+    tmin, tmax = verts.min(1), verts.max(1)
+    covered = np.zeros(N, np.int32)
+    seen = np.zeros(h["num_nodes4"], np.int32)
+    worst = [0]
+
+    def walk(r, stack):
+        seen[r] += 1
+        interior = int(((cnt[r] == 0) & (ref[r] >= 0)).sum())
+        stack += max(interior - 1, 0)
+        worst[0] = max(worst[0], stack)
+        lo_all, hi_all, prev_end = N, 0, None
+        for k in range(4):
+            c, hh = box[r, k >> 1, 0:3, k & 1], box[r, k >> 1, 3:6, k & 1]
+            if ref[r, k] < 0:                                          # empty slot: only after the used ones, never hit
+                assert cnt[r, k] == 0 and (hh < -1e29).all() and k >= 2
+                continue
+            if cnt[r, k] > 0:
+                a, b = int(ref[r, k]), int(ref[r, k] + cnt[r, k])
+                assert cnt[r, k] <= h["max_leaf"]
+                covered[a:b] += 1
+            else:
+                a, b = walk(int(ref[r, k]), stack)
+            assert (c - hh <= tmin[a:b].min(0)).all() and (c + hh >= tmax[a:b].max(0)).all()
+            assert prev_end is None or a == prev_end                   # ascending and adjacent
+            prev_end = b
+            lo_all, hi_all = min(lo_all, a), max(hi_all, b)
+        return lo_all, hi_all
+
+    import sys
+    sys.setrecursionlimit(10000)
+    assert walk(0, 0) == (0, N) and (covered == 1).all() and (seen == 1).all()
+    assert worst[0] <= 64
 
 
 def test_flatten_rejects_bad_input(rt, lib, sim):

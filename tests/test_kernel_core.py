@@ -261,6 +261,30 @@ def test_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, sim, scene, kw):
         assert wide["counters"][k] == binary["counters"][k], k
 
 
+def test_pow_specular_matches_libm(sim):
+    """pow_specular (own ln/exp for the Phong term, mytracer.cpp:525-533) against libm's pow on its domain: base in
+    [0, 1] (+ rounding above 1), positive exponent.  Relative error <= 1e-13 wherever the result is not negligible
+    (> 1e-200), exact special values, and values outside the fast domain fall back to pow() itself."""
+    import math
+    rng = np.random.default_rng(3)
+    worst = 0.0
+    for i in range(20000):
+        mode = i % 5
+        x = [rng.random(), 1.0 - rng.random() * 1e-3, 10.0 ** (-rng.random() * 20), 1.0 - rng.random() ** 2,
+             1.0 + (rng.random() - 0.5) * 1e-15][mode]
+        y = [0.3, 1, 2, 5, 10, 32, 50, 100, 128, 150, 200, 500][i % 12] * (0.5 + rng.random())
+        want = math.pow(x, y)
+        got = sim.pow_specular(x, y)
+        if want > 1e-200:
+            worst = max(worst, abs(got - want) / want)
+        else:
+            assert abs(got - want) <= 1e-200
+    assert worst < 1e-13
+    assert sim.pow_specular(0.0, 7.0) == 0.0 and sim.pow_specular(1.0, 123.0) == 1.0 and sim.pow_specular(0.5, 2.0) == 0.25
+    for x, y in ((1e-310, 0.5), (0.3, 1e5), (2.5, 3.0), (0.5, -2.0), (0.0, 0.0)):      # outside the fast domain
+        assert sim.pow_specular(x, y) == math.pow(x, y)
+
+
 def test_object_tree_keeps_list_order_semantics(rt, lib, sim, orc, oracle_kind):
     """Spheres go into their own tree when there are >= 8 of them; the reference loops over objects_ in list order
     with a strict '<'.  Duplicated spheres (equal t: the lower index must win), a sphere around the camera (ray
