@@ -169,7 +169,7 @@ typedef struct rt_scene_info {
   double flatten_ms, upload_ms;
   int topology;            /* 0: SAH traversal tree + reference tree for d.x == 0 rays; 1: reference tree only */
   int num_nodes_traversal; /* records of the tree ordinary rays walk */
-  int num_nodes_wide;      /* 128-byte four-child records of its 4-wide twin (0: none, e.g. scenes with an object tree) */
+  int num_nodes_wide;      /* 128-byte four-child records of the 4-wide twins of the traversal trees (0: none) */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene;

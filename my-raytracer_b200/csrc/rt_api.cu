@@ -62,7 +62,7 @@ struct rt_scene {
   int *d_list = nullptr; // supersampling pixel list
   size_t cap_list = 0;
   int grid_plain = 0, grid_count = 0;
-  int grid_wide = 0, grid_wide_count = 0; // K_WIDE kernels (scenes with a 4-wide tree and no object tree)
+  int grid_wide = 0, grid_wide_count = 0; // K_WIDE kernels (scenes whose trees all have 4-wide twins)
   bool wide_ok = false;
   int sm_count = 0, ctas_per_sm = 0; // ctas_per_sm: 0 = every resident slot (rt_scene_set_launch_width)
   size_t extra_smem = 0;
@@ -111,6 +111,7 @@ int adopt_blob(rt_scene *s) {
   s->view.obj_root = h.obj_root; s->view.num_lin = h.num_lin;
   s->view.tri_nodes = h.q_base + h.num_nodes_q;
   s->view.num_nodes4 = h.num_nodes4;
+  s->view.obj_root4 = h.obj_root4; s->view.num_nodes4_tri = h.num_nodes4_tri;
   s->view.nodes4 = h.num_nodes4 > 0 ? reinterpret_cast<const Node4Rec *>(b + h.off_nodes4) : nullptr;
   s->view.texels = reinterpret_cast<const float *>(b + h.off_texels);
   s->view.num_nodes = h.num_nodes; s->view.num_tris = h.num_tris;
@@ -177,11 +178,12 @@ int adopt_blob(rt_scene *s) {
   RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_count, kBlockThreads, s->extra_smem));
   // the 4-wide tree is walked by its own kernel variants; RT_B200_WIDE=0 (or RT_FLAG_BINARY_NODES per frame)
   // keeps ordinary rays on the binary tree
-  s->wide_ok = h.num_nodes4 > 0 && !obj;
+  s->wide_ok = wide_usable(s->view);
   if (const char *e = std::getenv("RT_B200_WIDE")) if (std::atoi(e) == 0) s->wide_ok = false;
   if (s->wide_ok) {
     int occ2 = 0, occ3 = 0;
-    const void *k_w = (const void *)render_kernel<K_WIDE>, *k_wc = (const void *)render_kernel<K_WIDE | K_COUNT>;
+    const void *k_w = obj ? (const void *)render_kernel<K_WIDE | K_OBJ> : (const void *)render_kernel<K_WIDE>;
+    const void *k_wc = obj ? (const void *)render_kernel<K_WIDE | K_OBJ | K_COUNT> : (const void *)render_kernel<K_WIDE | K_COUNT>;
     if (s->extra_smem) {
       RT_CUDA(cudaFuncSetAttribute(k_w, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
       RT_CUDA(cudaFuncSetAttribute(k_wc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
@@ -249,14 +251,15 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
     gp = gp < lim ? gp : lim;
   }
   const bool obj = s->hdr.obj_root >= 0; // tree over analytic spheres: the kernel variant that can walk it
-  if (count) {
-    if (obj) render_kernel<K_COUNT | K_OBJ><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
-    else if (wide) render_kernel<K_COUNT | K_WIDE><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
-    else render_kernel<K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a);
-  } else {
-    if (obj) render_kernel<K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
-    else if (wide) render_kernel<K_WIDE><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
-    else render_kernel<0><<<gp, kBlockThreads, s->extra_smem, st>>>(a);
+  switch ((count ? K_COUNT : 0) | (obj ? K_OBJ : 0) | (wide ? K_WIDE : 0)) {
+    case 0: render_kernel<0><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+    case K_COUNT: render_kernel<K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
+    case K_OBJ: render_kernel<K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+    case K_OBJ | K_COUNT: render_kernel<K_OBJ | K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
+    case K_WIDE: render_kernel<K_WIDE><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+    case K_WIDE | K_COUNT: render_kernel<K_WIDE | K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
+    case K_WIDE | K_OBJ: render_kernel<K_WIDE | K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+    default: render_kernel<K_WIDE | K_OBJ | K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
   }
   RT_CUDA(cudaGetLastError());
   RT_CUDA(cudaEventRecord(s->ev1[slot], st));

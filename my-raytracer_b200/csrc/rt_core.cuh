@@ -85,7 +85,8 @@ enum Special : int { S_XPAR = 1, S_OBJ = 2 };
 // Kernel configuration bits (the template parameter named COUNT throughout): K_COUNT = instrumented build,
 // K_OBJ = the scene has a tree over analytic spheres.  Scenes without one run a kernel that contains none of
 // that code (its mere presence in the leaf path costs 3 % on the Office scene).
-// K_WIDE = ordinary rays walk the 4-wide tree (Node4Rec, trav_step4); never combined with K_OBJ.
+// K_WIDE = ordinary rays walk the 4-wide twins of the traversal trees (Node4Rec, trav_step4): the triangle tree's
+// and, with K_OBJ, the object tree's (the host picks K_WIDE only when every tree the scene has owns a twin).
 enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2, K_WIDE = 4 };
 
 struct Mat {
@@ -259,7 +260,7 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   if ((COUNT & K_OBJ) && sv.obj_root >= 0) {
     // spheres first (the reference tests objects_ before the meshes): walk their tree, then the triangles
     H.special |= S_OBJ;
-    H.node = sv.obj_root;
+    H.node = (COUNT & K_WIDE) ? sv.obj_root4 : sv.obj_root;
   } else {
     enter_triangles(c, H, C);
   }

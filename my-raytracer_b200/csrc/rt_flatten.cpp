@@ -251,11 +251,81 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     for (TriFilter &f : filt) f.k_det = std::numeric_limits<float>::infinity();
   }
 
+  // 4-wide twin of a binary SAH tree (rt_types.h Node4Rec): a binary node's two children, then repeatedly the interior
+  // child with the largest surface area replaced IN PLACE by its own two children (so the children stay in the binary
+  // tree's left-to-right order and leaf ranges ascend) until there are four or none is interior.  Records are appended
+  // to `out` in DFS pre-order; returns the root's record index.  The kernel pushes at most (interior children - 1)
+  // entries per visit; if the worst root-to-leaf sum does not fit the traversal stack the twin is dropped (-1).
+  auto collapse_wide = [&](const std::vector<SahNode> &sn, std::vector<Node4Rec> &out) -> int {
+    struct W4 { int sah_node, rec, stack_before; };
+    std::vector<W4> todo4;
+    const size_t base4 = out.size();
+    out.emplace_back();
+    todo4.push_back({0, (int)base4, 0});
+    int worst_stack = 0;
+    auto area = [&](int k) {
+      const SahNode &b = sn[k];
+      const double dx = (double)b.hi[0] - b.lo[0], dy = (double)b.hi[1] - b.lo[1], dz = (double)b.hi[2] - b.lo[2];
+      return dx * dy + dy * dz + dz * dx;
+    };
+    while (!todo4.empty()) {
+      const W4 w = todo4.back();
+      todo4.pop_back();
+      int slot[4], ns = 2;
+      slot[0] = sn[w.sah_node].left; slot[1] = sn[w.sah_node].right;
+      while (ns < 4) {
+        int pick = -1;
+        double best_area = -1.0;
+        for (int k = 0; k < ns; ++k)
+          if (sn[slot[k]].count == 0 && area(slot[k]) > best_area) { best_area = area(slot[k]); pick = k; }
+        if (pick < 0) break;
+        const int l = sn[slot[pick]].left, r = sn[slot[pick]].right;
+        for (int k = ns; k > pick + 1; --k) slot[k] = slot[k - 1];
+        slot[pick] = l; slot[pick + 1] = r;
+        ++ns;
+      }
+      Node4Rec n;
+      int child_rec[4] = {-1, -1, -1, -1}, interior = 0;
+      for (int k = 0; k < 4; ++k) {
+        float ctr[3] = {0.0f, 0.0f, 0.0f}, half[3] = {-1e30f, -1e30f, -1e30f};
+        if (k < ns) {
+          const SahNode &cb = sn[slot[k]];
+          const double lo[3] = {cb.lo[0], cb.lo[1], cb.lo[2]}, hi[3] = {cb.hi[0], cb.hi[1], cb.hi[2]};
+          box_lohi(lo, hi, ctr, half);
+        }
+        for (int a = 0; a < 3; ++a) n.box[k >> 1][a][k & 1] = ctr[a], n.box[k >> 1][3 + a][k & 1] = half[a];
+        if (k >= ns) {
+          n.ref[k] = -1; n.cnt[k] = 0;
+          continue;
+        }
+        const SahNode &cn = sn[slot[k]];
+        if (cn.count > 0) { n.ref[k] = cn.first; n.cnt[k] = cn.count; }
+        else {
+          child_rec[k] = (int)out.size();
+          out.emplace_back();
+          n.ref[k] = child_rec[k]; n.cnt[k] = 0;
+          ++interior;
+        }
+      }
+      const int stack_after = w.stack_before + (interior > 1 ? interior - 1 : 0);
+      if (stack_after > worst_stack) worst_stack = stack_after;
+      for (int k = 3; k >= 0; --k)
+        if (child_rec[k] >= 0) todo4.push_back({slot[k], child_rec[k], stack_after});
+      out[w.rec] = n;
+    }
+    if (worst_stack > kStackMax || out.size() >= ((size_t)1 << 27)) { // (record << 4 | mask) must fit an int
+      out.resize(base4);
+      return -1;
+    }
+    return (int)base4;
+  };
+
   // ---- 2b. the traversal tree (rt_sah.h): SAH over the same triangles, reference tree kept for the quirk ----
   std::vector<int> tri_id(N), tri_pos(N);
   for (int i = 0; i < N; ++i) tri_id[i] = tri_pos[i] = i;
   int q_base = 0, topology = 1;
   std::vector<Node4Rec> wide;
+  int wide_tri = 0, obj_root4 = -1; // records of the triangle twin (root = record 0); root of the object-tree twin
   const int num_nodes_q = (int)nodes.size();
   if (!(flags & RT_SCENE_REFERENCE_TOPOLOGY) && N > 2 && !root_is_leaf) {
     std::vector<float> plo(3 * (size_t)N), phi(3 * (size_t)N);
@@ -302,69 +372,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
         trav[w.flat_idx] = n;
       }
       if (sah_depth > max_depth) max_depth = sah_depth;
-      // 4-wide twin of the same tree: a binary node's two children, then repeatedly the interior child with the
-      // largest surface area replaced IN PLACE by its own two children (so the children stay in the binary
-      // tree's left-to-right order and leaf ranges ascend) until there are four or none is interior.
-      // Records in DFS pre-order.  The kernel pushes at most (interior children - 1) entries per visit; if the
-      // worst root-to-leaf sum does not fit the traversal stack the wide tree is dropped (binary tree stays).
-      {
-        struct W4 { int sah_node, rec, stack_before; };
-        std::vector<W4> todo4;
-        wide.emplace_back();
-        todo4.push_back({0, 0, 0});
-        int worst_stack = 0;
-        auto area = [&](int k) {
-          const SahNode &b = sn[k];
-          const double dx = (double)b.hi[0] - b.lo[0], dy = (double)b.hi[1] - b.lo[1], dz = (double)b.hi[2] - b.lo[2];
-          return dx * dy + dy * dz + dz * dx;
-        };
-        while (!todo4.empty()) {
-          const W4 w = todo4.back();
-          todo4.pop_back();
-          int slot[4], ns = 2;
-          slot[0] = sn[w.sah_node].left; slot[1] = sn[w.sah_node].right;
-          while (ns < 4) {
-            int pick = -1;
-            double best_area = -1.0;
-            for (int k = 0; k < ns; ++k)
-              if (sn[slot[k]].count == 0 && area(slot[k]) > best_area) { best_area = area(slot[k]); pick = k; }
-            if (pick < 0) break;
-            const int l = sn[slot[pick]].left, r = sn[slot[pick]].right;
-            for (int k = ns; k > pick + 1; --k) slot[k] = slot[k - 1];
-            slot[pick] = l; slot[pick + 1] = r;
-            ++ns;
-          }
-          Node4Rec n;
-          int child_rec[4] = {-1, -1, -1, -1}, interior = 0;
-          for (int k = 0; k < 4; ++k) {
-            float ctr[3] = {0.0f, 0.0f, 0.0f}, half[3] = {-1e30f, -1e30f, -1e30f};
-            if (k < ns) {
-              const SahNode &cb = sn[slot[k]];
-              const double lo[3] = {cb.lo[0], cb.lo[1], cb.lo[2]}, hi[3] = {cb.hi[0], cb.hi[1], cb.hi[2]};
-              box_lohi(lo, hi, ctr, half);
-            }
-            for (int a = 0; a < 3; ++a) n.box[k >> 1][a][k & 1] = ctr[a], n.box[k >> 1][3 + a][k & 1] = half[a];
-            if (k >= ns) {
-              n.ref[k] = -1; n.cnt[k] = 0;
-              continue;
-            }
-            const SahNode &cn = sn[slot[k]];
-            if (cn.count > 0) { n.ref[k] = cn.first; n.cnt[k] = cn.count; }
-            else {
-              child_rec[k] = (int)wide.size();
-              wide.emplace_back();
-              n.ref[k] = child_rec[k]; n.cnt[k] = 0;
-              ++interior;
-            }
-          }
-          const int stack_after = w.stack_before + (interior > 1 ? interior - 1 : 0);
-          if (stack_after > worst_stack) worst_stack = stack_after;
-          for (int k = 3; k >= 0; --k)
-            if (child_rec[k] >= 0) todo4.push_back({slot[k], child_rec[k], stack_after});
-          wide[w.rec] = n;
-        }
-        if (worst_stack > kStackMax || wide.size() >= ((size_t)1 << 27)) wide.clear(); // (record << 4 | mask) must fit an int
-      }
+      wide_tri = collapse_wide(sn, wide) == 0 ? (int)wide.size() : 0;
       q_base = (int)trav.size();
       topology = 0;
       for (NodeRec &r : nodes) { // reference tree: interior child references move behind the traversal tree
@@ -497,6 +505,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
         if (depth > max_depth) max_depth = depth;
         obj_root = base;
         num_nodes_obj = (int)trav.size();
+        obj_root4 = collapse_wide(sn, wide);
         nodes.insert(nodes.end(), trav.begin(), trav.end());
         obj_order.resize(ns);
         for (int j = 0; j < ns; ++j) obj_order[j] = sph[order[j]];
@@ -536,6 +545,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.off_lin_idx = off; off = align_up(off + lin_idx.size() * sizeof(int32_t), kSectionAlign);
   h.off_nodes4 = off;  off = align_up(off + wide.size() * sizeof(Node4Rec), kSectionAlign);
   h.num_nodes4 = (int)wide.size();
+  h.num_nodes4_tri = wide_tri; h.obj_root4 = obj_root4;
   h.obj_root = obj_root; h.num_nodes_obj = num_nodes_obj; h.num_obj_tree = (int)obj_order.size(); h.num_lin = (int)lin_idx.size();
   h.q_base = q_base; h.num_nodes_q = num_nodes_q; h.topology = topology;
   h.root_max_x = N > 0 ? bvh->bb_max_[0].x : 0.0;
@@ -584,7 +594,8 @@ int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
                   h.off_objfilt + (size_t)h.num_objects * sizeof(ObjFilter) <= h.off_obj_order &&
                   h.off_obj_order + (size_t)h.num_obj_tree * sizeof(int32_t) <= h.off_lin_idx &&
                   h.off_lin_idx + (size_t)h.num_lin * sizeof(int32_t) <= h.off_nodes4 &&
-                  h.num_nodes4 >= 0 && h.off_nodes4 % 32 == 0 &&
+                  h.num_nodes4 >= 0 && h.off_nodes4 % 32 == 0 && h.num_nodes4_tri >= 0 && h.num_nodes4_tri <= h.num_nodes4 &&
+                  h.obj_root4 >= -1 && h.obj_root4 < (h.num_nodes4 > 0 ? h.num_nodes4 : 1) &&
                   h.off_nodes4 + (size_t)h.num_nodes4 * sizeof(Node4Rec) <= h.total_bytes &&
                   h.num_nodes_obj >= 0 && h.num_obj_tree >= 0 && h.num_lin >= 0 && h.num_obj_tree + h.num_lin == h.num_objects &&
                   (h.obj_root < 0 ? h.num_nodes_obj == 0 : h.obj_root == h.q_base + h.num_nodes_q) &&
@@ -609,6 +620,7 @@ SceneView view_of_blob(const unsigned char *blob) {
   v.obj_root = h.obj_root; v.num_lin = h.num_lin;
   v.tri_nodes = h.q_base + h.num_nodes_q;
   v.num_nodes4 = h.num_nodes4;
+  v.obj_root4 = h.obj_root4; v.num_nodes4_tri = h.num_nodes4_tri;
   v.nodes4 = h.num_nodes4 > 0 ? reinterpret_cast<const Node4Rec *>(blob + h.off_nodes4) : nullptr;
   v.texels = reinterpret_cast<const float *>(blob + h.off_texels);
   v.tex_objs = nullptr;

@@ -41,7 +41,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 10;
+constexpr uint32_t kBlobVersion = 11;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -160,7 +160,11 @@ struct BlobHeader {
   uint64_t off_lin_idx;   // int32[num_lin]: objects tested linearly, in list order
   int32_t obj_root;       // record index of the object tree's root, -1: no object tree
   int32_t num_nodes_obj, num_obj_tree, num_lin;
-  uint64_t off_nodes4;    // Node4Rec[num_nodes4]
+  uint64_t off_nodes4;    // Node4Rec[num_nodes4]: the 4-wide twin of the triangle traversal tree first (root = record 0,
+                          // num_nodes4_tri records), then the twin of the object tree (root = obj_root4)
+  int32_t num_nodes4_tri; // 0: the triangle tree has no 4-wide twin
+  int32_t obj_root4;      // -1: the object tree has none
+  int32_t pad_h[2];
 };
 static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
 
@@ -183,12 +187,23 @@ struct SceneView {
   const int32_t *lin_idx;   // objects tested linearly at ray start
   int32_t obj_root, num_lin;
   int32_t tri_nodes;        // records of the triangle trees (0: the scene has no triangles)
-  int32_t num_nodes4;       // records of the 4-wide tree (0: none)
+  int32_t num_nodes4;       // records of the 4-wide trees (0: none)
+  int32_t obj_root4;        // root of the object tree's 4-wide twin in nodes4 (-1: none)
+  int32_t num_nodes4_tri;   // records of the triangle tree's twin (root = record 0; 0: none)
   double root_max_x;
   int32_t num_nodes, num_tris, num_meshes, num_objects;
   float box_extent;
   int32_t q_base;
 };
+
+// The K_WIDE kernels walk 4-wide records only (plus the reference tree for d.x == 0 rays): usable when every tree
+// ordinary rays walk has a twin — the triangle tree (if the scene has one that is not the reference topology itself)
+// and the object tree (if the scene has one).
+inline bool wide_usable(const SceneView &v) {
+  const bool tri_ok = v.tri_nodes == 0 || v.num_nodes4_tri > 0;
+  const bool obj_ok = v.obj_root < 0 || v.obj_root4 >= 0;
+  return v.num_nodes4 > 0 && tri_ok && obj_ok;
+}
 
 struct CameraRec {
   double eye[3], x_dir[3], y_dir[3], lower_left[3];

@@ -85,13 +85,14 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
       }
       Hot H;
       H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0; H.pend = 0;
-      // the same choice of kernel variant as rt_api.cu launch(): the 4-wide tree when the blob has one, the scene
-      // has no object tree and the frame does not ask for the binary nodes
-      if (ct.sv.num_nodes4 > 0 && ct.sv.obj_root < 0 && !(ct.fp.flags & RT_FLAG_BINARY_NODES)) {
-        begin_pixel<K_COUNT | K_WIDE>(ct, H, Cd, px, py);
+      // the same choice of kernel variant as rt_api.cu launch(): the 4-wide twins when every tree of the scene has one
+      // and the frame does not ask for the binary records
+      const bool wide = wide_usable(ct.sv) && !(ct.fp.flags & RT_FLAG_BINARY_NODES);
+      if (wide) {
+        begin_pixel<K_COUNT | K_OBJ | K_WIDE>(ct, H, Cd, px, py);
         while (H.mode != M_IDLE) {
-          if (H.node != -1) traverse<K_COUNT | K_WIDE>(ct, H, Cd, stk);
-          else advance<K_COUNT | K_WIDE>(ct, H, Cd);
+          if (H.node != -1) traverse<K_COUNT | K_OBJ | K_WIDE>(ct, H, Cd, stk);
+          else advance<K_COUNT | K_OBJ | K_WIDE>(ct, H, Cd);
         }
       } else {
         begin_pixel<K_COUNT | K_OBJ>(ct, H, Cd, px, py);

@@ -90,6 +90,8 @@ def test_frame_does_not_depend_on_the_tree(rt, lib, gpu, name, kw):
     ("scatter", dict(width=256, height=144, n_objects=300)),      # d.x == 0 rays stay on the reference tree
     ("textured", dict(width=256, height=144, tex_size=256, slices=64, stacks=32)),
     ("rings", dict(width=200, height=150)),
+    ("molecule", dict(width=200, height=200, n_spheres=300)),     # object tree only: its 4-wide twin
+    ("objtree", dict(width=192, height=144)),                      # object tree + triangles, list-order ties
 ])
 def test_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, gpu, name, kw):
     """The 4-wide twin of the traversal tree (render_kernel<K_WIDE>, default) against the binary tree it is
@@ -108,7 +110,8 @@ def test_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, gpu, name, kw):
         for k in ("hit_id", "hit_t", "rgba8", "pixels"):
             assert np.array_equal(wide[k], other[k]), k
     assert wide_c["counters"]["nodes4_visited"] > 0 and binary_c["counters"]["nodes4_visited"] == 0
-    assert wide_c["counters"]["nodes_visited"] < 0.75 * binary_c["counters"]["nodes_visited"]
+    ratio = 1.0 if name == "objtree" else 0.75           # objtree: a dozen spheres and a few triangles, tiny trees
+    assert wide_c["counters"]["nodes_visited"] < ratio * binary_c["counters"]["nodes_visited"]
     for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
         assert wide_c["counters"][k] == binary_c["counters"][k], k
 

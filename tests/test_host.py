@@ -222,7 +222,7 @@ def test_wide_tree_structure(rt, lib, sim):
     blob = sim.flatten(host)
     h = _blob_sections(blob)
     N = 34000
-    assert h["version"] == 10 and h["num_nodes4"] > 0 and h["off_nodes4"] % 32 == 0
+    assert h["version"] == 11 and h["num_nodes4"] > 0 and h["off_nodes4"] % 32 == 0
     assert h["off_nodes4"] + 128 * h["num_nodes4"] <= h["total"]
     assert h["num_nodes4"] < 0.6 * h["q_base"]                       # at least ~2 binary records per wide record
     rec = np.frombuffer(blob, np.float32, h["num_nodes4"] * 32, h["off_nodes4"]).reshape(-1, 32)

@@ -242,7 +242,9 @@ def test_frame_does_not_depend_on_the_tree(rt, lib, sim, scene, kw):
 @pytest.mark.parametrize("scene,kw", [("office", dict(width=128, height=72)),
                                       ("scatter", dict(width=81, height=61, n_objects=40)),
                                       ("rings", dict(width=70, height=50, nu=48, nv=16)),
-                                      ("textured", dict(width=96, height=54, tex_size=64, slices=24, stacks=12))])
+                                      ("textured", dict(width=96, height=54, tex_size=64, slices=24, stacks=12)),
+                                      ("molecule", dict(width=90, height=90, n_spheres=150)),     # object tree only
+                                      ("objtree", dict(width=96, height=72))])                    # object tree + triangles
 def test_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, sim, scene, kw):
     """The 4-wide twin of the traversal tree (Node4Rec, trav_step4) against the binary tree it is collapsed from
     (RT_FLAG_BINARY_NODES): bit-identical ids, distances and FP64 pixels, fewer node visits; and the FP32 filter
@@ -256,7 +258,8 @@ def test_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, sim, scene, kw):
     for k in ("hit_id", "hit_t", "rgba8", "pixels"):
         assert np.array_equal(wide[k], binary[k]), k
         assert np.array_equal(wide[k], exact[k]), k
-    assert wide["counters"]["nodes_visited"] < 0.75 * binary["counters"]["nodes_visited"]
+    ratio = 1.0 if scene == "objtree" else 0.75          # objtree: a dozen spheres and a few triangles, tiny trees
+    assert wide["counters"]["nodes_visited"] < ratio * binary["counters"]["nodes_visited"]
     for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
         assert wide["counters"][k] == binary["counters"][k], k
 
