@@ -76,7 +76,6 @@ struct Hot {
   int sp;
   int mode;
   int found;   // any-hit result
-  int pend;    // K_WIDE with RT_DEFER_LEAF: (Node4Rec index << 4) | mask of its hit leaf children, not tested yet
   int special; // rare-path flags, tested with ONE predicate in the hot loop:
                //   S_XPAR: direction.x == 0 exactly, the reference's 0/0 slab quirk applies (rt_types.h NodeMaxX)
                //   S_OBJ : the ray is walking the tree over the analytic spheres (before the triangle tree)
@@ -227,7 +226,6 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   H.best_id = -1;
   H.found = 0;
   H.sp = 0;
-  H.pend = 0;
   double best = tmax;
   float othi = thi_of(best);
   const bool exact_only = (c.fp.flags & 1) != 0;
@@ -411,12 +409,9 @@ template <int COUNT, bool XP, int S> RT_HD void trav_step(const Ctx &c, Hot &H, 
 }
 
 // One step through the 4-wide tree (K_WIDE kernels, ordinary rays only): one 128-byte Node4Rec (four 32-byte
-// loads), four independent conservative slab tests (48 FMAs as 24 FFMA2, box_pair), hit leaf children intersected at once, the nearest
-// hit interior child next, the others pushed with their entry distances (culled when popped).  Half the
+// loads), four independent conservative slab tests (48 FMAs as 24 FFMA2, box_pair), hit leaf children intersected at
+// once, the nearest hit interior child next, the others pushed with their entry distances (culled when popped).  Half the
 // dependent load -> test -> branch chains of the binary step per ray, twice the independent work inside one.
-#ifndef RT_DEFER_LEAF
-#define RT_DEFER_LEAF 0 // N > 0: leaf tests start when N lanes wait with pending leaves (33: all).  Measured: a loss (1.61-1.64 vs 1.56 ms, profiles/r01_variants.md)
-#endif
 RT_HD int first_bit(unsigned m) {
 #if defined(__CUDA_ARCH__)
   return __ffs((int)m) - 1;
@@ -424,17 +419,6 @@ RT_HD int first_bit(unsigned m) {
   int k = 0;
   while (!((m >> k) & 1u)) ++k;
   return k;
-#endif
-}
-// experiment (RT_PREFETCH_PUSH): pull a postponed child's record towards the SM when it is pushed
-#ifndef RT_PREFETCH_PUSH
-#define RT_PREFETCH_PUSH 0
-#endif
-RT_HD void prefetch_node4(const Ctx &c, int ref) {
-#if RT_PREFETCH_PUSH && defined(__CUDA_ARCH__)
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const char *>(c.sv.nodes4) + (size_t)(unsigned)ref * 128u));
-#else
-  (void)c; (void)ref;
 #endif
 }
 // The hit leaf children [first, last) ranges of one Node4Rec (refs r*, counts n*, mask lm), ascending; neighbours own
@@ -455,19 +439,7 @@ RT_HD void wide_leaves(const Ctx &c, Hot &H, const Cold<S> &C, unsigned lm, int 
     if (H.found) { H.node = -1; return; }
   } while (lm);
 }
-// Deferred leaves (RT_DEFER_LEAF): the triangle tests of a step run at ~12 of 32 lanes when every lane tests its
-// leaves the moment it finds them.  Instead the lane notes (record, mask) in H.pend, finishes the step (the
-// interior children are ordered and pushed as usual) and WAITS; when enough lanes of the warp wait — or nobody
-// can step — they test their leaves together.  The postponed test only delays the shrinking of thiS (a
-// conservative bound), so the frame is unchanged.
-template <int COUNT, int S> RT_HD void wide_pending_leaves(const Ctx &c, Hot &H, const Cold<S> &C) {
-  const unsigned pend = (unsigned)H.pend;
-  H.pend = 0;
-  const W8 q3 = ld_w8(reinterpret_cast<const char *>(c.sv.nodes4) + (size_t)(pend >> 4) * 128u + 96u);
-  wide_leaves<COUNT>(c, H, C, pend & 15u, (int)q3.w[0], (int)q3.w[1], (int)q3.w[2], (int)q3.w[3], (int)q3.w[4],
-                     (int)q3.w[5], (int)q3.w[6], (int)q3.w[7]);
-}
-template <int COUNT, bool DEFER, int S>
+template <int COUNT, int S>
 RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   const char *np = reinterpret_cast<const char *>(c.sv.nodes4) + (size_t)(unsigned)H.node * 128u;
   const W8 q0 = ld_w8(np), q1 = ld_w8(np + 32), q2 = ld_w8(np + 64), q3 = ld_w8(np + 96);
@@ -487,12 +459,8 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   unsigned lm = (h0 && n0 > 0 ? 1u : 0u) | (h1 && n1 > 0 ? 2u : 0u) | (h2 && n2 > 0 ? 4u : 0u) | (h3 && n3 > 0 ? 8u : 0u);
   if (lm) {
     h0 = h0 && !(lm & 1u); h1 = h1 && !(lm & 2u); h2 = h2 && !(lm & 4u); h3 = h3 && !(lm & 8u);
-    if (DEFER) {
-      H.pend = (int)(((unsigned)H.node << 4) | lm);
-    } else {
-      wide_leaves<COUNT>(c, H, C, lm, r0, r1, r2, r3, n0, n1, n2, n3);
-      if (H.found) return;
-    }
+    wide_leaves<COUNT>(c, H, C, lm, r0, r1, r2, r3, n0, n1, n2, n3);
+    if (H.found) return;
     // a nearer hit may have been found: surviving interior children are re-checked when visited / popped
   }
   int node, sp = H.sp;
@@ -503,10 +471,10 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
     // nearest interior child next (first of equals); the others are pushed in child order (no branches)
     const bool k0 = u0 == m, k1 = !k0 && u1 == m, k2 = !k0 && !k1 && u2 == m;
     node = k0 ? r0 : (k1 ? r1 : (k2 ? r2 : r3));
-    if (h0 && !k0) { stk[sp].ref = r0; stk[sp].tn = t0; ++sp; prefetch_node4(c, r0); }
-    if (h1 && !k1) { stk[sp].ref = r1; stk[sp].tn = t1; ++sp; prefetch_node4(c, r1); }
-    if (h2 && !k2) { stk[sp].ref = r2; stk[sp].tn = t2; ++sp; prefetch_node4(c, r2); }
-    if (h3 && (k0 || k1 || k2)) { stk[sp].ref = r3; stk[sp].tn = t3; ++sp; prefetch_node4(c, r3); }
+    if (h0 && !k0) { stk[sp].ref = r0; stk[sp].tn = t0; ++sp; }
+    if (h1 && !k1) { stk[sp].ref = r1; stk[sp].tn = t1; ++sp; }
+    if (h2 && !k2) { stk[sp].ref = r2; stk[sp].tn = t2; ++sp; }
+    if (h3 && (k0 || k1 || k2)) { stk[sp].ref = r3; stk[sp].tn = t3; ++sp; }
   } else {
     node = -1;
     while (sp > 0) {
@@ -523,12 +491,7 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
 template <int COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   do {
     if (COUNT & K_WIDE) {
-      // ordinary rays; d.x == 0 rays are parked (node <= -2).  One lane: the deferred leaves are tested right after
-      // the step that found them (the kernel batches them across the warp, rt_kernel.cuh)
-      while (H.node >= 0 || H.pend) {
-        if (H.pend) wide_pending_leaves<COUNT>(c, H, C);
-        else trav_step4<COUNT, RT_DEFER_LEAF != 0>(c, H, C, stk);
-      }
+      while (H.node >= 0) trav_step4<COUNT>(c, H, C, stk); // ordinary rays; d.x == 0 rays are parked (node <= -2)
     }
     unpark(H.node);
     while (H.node >= 0) trav_step<COUNT, true>(c, H, C, stk);

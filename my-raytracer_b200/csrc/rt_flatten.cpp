@@ -313,7 +313,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
         if (child_rec[k] >= 0) todo4.push_back({slot[k], child_rec[k], stack_after});
       out[w.rec] = n;
     }
-    if (worst_stack > kStackMax || out.size() >= ((size_t)1 << 27)) { // (record << 4 | mask) must fit an int
+    if (worst_stack > kStackMax || out.size() >= ((size_t)1 << 30)) {
       out.resize(base4);
       return -1;
     }

@@ -90,7 +90,6 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
   H.found = 0;
   H.best_id = -1;
   H.special = 0;
-  H.pend = 0;
   const long long slots = work_slots(c);
   const long long nchunks = a.dyn_counter ? pool_chunks(c) : 0;
   const unsigned lane = threadIdx.x & 31u;
@@ -173,26 +172,9 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     for (;;) {
       if (COUNT & K_WIDE) {
         // ordinary rays walk the 4-wide tree: half the dependent steps, four independent box tests in each
-#if RT_DEFER_LEAF
-        // deferred leaves (rt_core.cuh wide_pending_leaves): lanes that found leaf children wait; the warp tests
-        // leaves when RT_DEFER_LEAF lanes wait or nobody can step
-        for (;;) {
-          const bool can = H.node >= 0 && H.pend == 0;
-          const unsigned stepping = __ballot_sync(kFullMask, can);
-          const unsigned waiting = __ballot_sync(kFullMask, H.pend != 0);
-          if (stepping != 0u && __popc(waiting) < RT_DEFER_LEAF) {
-            if (can) trav_step4<COUNT, true>(c, H, C, stk);
-          } else if (waiting != 0u) {
-            if (H.pend) wide_pending_leaves<COUNT>(c, H, C);
-          } else {
-            break;
-          }
-        }
-#else
         while (__any_sync(kFullMask, H.node >= 0)) {
-          if (H.node >= 0) trav_step4<COUNT, false>(c, H, C, stk);
+          if (H.node >= 0) trav_step4<COUNT>(c, H, C, stk);
         }
-#endif
       } else {
         while (__any_sync(kFullMask, H.node >= 0)) {
           if (H.node >= 0) trav_step<COUNT, false>(c, H, C, stk);

@@ -84,7 +84,7 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
         if (!pool_to_pixel(ct, s, px, py)) continue;
       }
       Hot H;
-      H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0; H.pend = 0;
+      H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0;
       // the same choice of kernel variant as rt_api.cu launch(): the 4-wide twins when every tree of the scene has one
       // and the frame does not ask for the binary records
       const bool wide = wide_usable(ct.sv) && !(ct.fp.flags & RT_FLAG_BINARY_NODES);
