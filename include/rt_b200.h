@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 4
+#define RT_B200_ABI_VERSION 5
 
 typedef enum rt_status {
   RT_OK = 0,
@@ -223,6 +223,46 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_vec4 *lights_po
 int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_vec4 *d_lights_pos,
                      const rt_vec4 *d_lights_color, int num_lights, const rt_render_params *params,
                      const rt_frame_out *out_device, void *stream);
+/* Launches of one scene may be in flight on several streams.  Each takes its work counter and event pair from a
+ * ring of 8 slots; launch f + 8 is ordered behind launch f (cudaStreamWaitEvent), so more than 8 frames in flight
+ * are safe but serialise.  RT_FLAG_COUNTERS launches are synchronous (the counters are read back before the
+ * call returns) and share one counter block: do not overlap them with each other. */
+/* ---- pipelined host-buffer frames --------------------------------------------------------------
+ * The body of Raytracer::compute_image_cuda() (mytracer.cpp:123-159: copyLights :105-118, the launch,
+ * the D2H copy mytracer_gpu.cu:112) for a host that renders a SEQUENCE of frames: up to `depth` frames are in
+ * flight, the D2H copy of frame f (own copy stream) overlaps the kernel of frame f + 1, and the caller's light
+ * arrays are staged so they may be reused as soon as rt_frame_submit returns.
+ *   rt_frame_submit   enqueues one frame; blocks only while `depth` earlier frames are still unfinished.
+ *                     rgba8_host: W*H*4 bytes, pinned (rt_host_alloc / rt_host_register) for an asynchronous copy.
+ *   rt_frame_wait     blocks until the frame of `ticket` (and every earlier one) is in rgba8_host; done_ms (may be
+ *                     NULL) = its completion time in ms on the queue's CUDA-event timeline (0 = first submit).
+ * opts.zero_copy: the render kernel stores finished pixels straight into rgba8_host (which must then be mapped
+ * pinned memory: rt_host_alloc / rt_host_register) - no staging buffer and no copy pass; with tile sharding
+ * (rt_render_params.tile_*) the ranks of a multi-GPU job fill ONE host frame in shared memory, each over its own
+ * PCIe link.  opts.flush_bytes: benchmark aid, a memset of that many bytes ahead of every frame evicts the L2. */
+typedef struct rt_frame_queue rt_frame_queue;
+typedef struct rt_frame_queue_opts {
+  int depth;           /* frames in flight, 1..32 (0 = 2) */
+  int ctas_per_sm;     /* persistent-grid width of each frame, see rt_scene_set_launch_width (0 = all) */
+  int zero_copy;
+  int pad_;
+  size_t flush_bytes;
+} rt_frame_queue_opts;
+int rt_frame_queue_create(rt_scene *scene, int width, int height, const rt_frame_queue_opts *opts,
+                          rt_frame_queue **out);
+int rt_frame_submit(rt_frame_queue *queue, const rt_camera *camera, const rt_vec4 *lights_pos,
+                    const rt_vec4 *lights_color, int num_lights, const rt_render_params *params,
+                    uint8_t *rgba8_host, long long *ticket);
+int rt_frame_wait(rt_frame_queue *queue, long long ticket, double *done_ms);
+int rt_frame_queue_destroy(rt_frame_queue *queue);
+/* Pinned, device-mapped host memory for frames: allocated here, or an existing block (e.g. a POSIX shared-memory
+ * segment that every rank's process maps) registered with the CUDA driver.  dptr (may be NULL): its device
+ * address, usable as rt_frame_out.rgba8 of rt_render_device. */
+int rt_host_alloc(size_t bytes, void **ptr);
+int rt_host_free(void *ptr);
+int rt_host_register(void *ptr, size_t bytes, void **dptr);
+int rt_host_unregister(void *ptr);
+
 /* ---- peer memory for the multi-GPU frame (one process per GPU) ---------------------------- */
 /* Device allocation that can be shared with the other ranks' processes (plain cudaMalloc, zero-filled):
  * rank 0 allocates the frame buffer and the dynamic-queue counters, exports 64-byte handles, the host

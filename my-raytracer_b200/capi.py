@@ -112,6 +112,11 @@ class SceneInfo(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class FrameQueueOpts(C.Structure):
+    _fields_ = [("depth", C.c_int), ("ctas_per_sm", C.c_int), ("zero_copy", C.c_int), ("pad_", C.c_int),
+                ("flush_bytes", C.c_size_t)]
+
+
 class SceneFileView(C.Structure):
     _fields_ = [("data", DataSoA), ("bvh", BvhNodesSoA), ("nodes_used", C.c_int), ("objects", C.POINTER(Object)),
                 ("num_objects", C.c_int), ("camera", Camera), ("lights_pos", Vec4_p), ("lights_color", Vec4_p),
@@ -140,6 +145,15 @@ PROTOTYPES = {
                             C.POINTER(FrameOut)]),
     "rt_render_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_int,
                                    C.POINTER(RenderParams), C.POINTER(FrameOut), C.c_void_p]),
+    "rt_frame_queue_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(FrameQueueOpts), C.POINTER(C.c_void_p)]),
+    "rt_frame_submit": (C.c_int, [C.c_void_p, C.POINTER(Camera), Vec4_p, Vec4_p, C.c_int, C.POINTER(RenderParams),
+                                  C.c_void_p, C.POINTER(C.c_longlong)]),
+    "rt_frame_wait": (C.c_int, [C.c_void_p, C.c_longlong, c_double_p]),
+    "rt_frame_queue_destroy": (C.c_int, [C.c_void_p]),
+    "rt_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    "rt_host_free": (C.c_int, [C.c_void_p]),
+    "rt_host_register": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
+    "rt_host_unregister": (C.c_int, [C.c_void_p]),
     "rt_shared_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "rt_shared_free": (C.c_int, [C.c_void_p]),
     "rt_ipc_export": (C.c_int, [C.c_void_p, c_ubyte_p]),
@@ -188,7 +202,7 @@ def load_library(path: str | None = None):
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.rt_abi_version() != 4:
+    if lib.rt_abi_version() != 5:
         raise RuntimeError("rt_b200 ABI version mismatch")
     if path is None:
         _lib = lib

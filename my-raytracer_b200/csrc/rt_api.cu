@@ -47,6 +47,7 @@ struct rt_scene {
   cudaEvent_t ev0[kRing] = {}, ev1[kRing] = {};
   unsigned long long *d_work = nullptr; // kRing x {slot counter, pool-empty flag}
   unsigned launch_seq = 0;
+  bool slot_used[kRing] = {};
   int last_slot = 0;
   unsigned long long *d_counters = nullptr;
   double *d_lights = nullptr; // pos[4*n] then col[4*n]
@@ -84,15 +85,57 @@ int ensure_device(std::string &err) {
   return RT_OK;
 }
 
-template <typename T> int ensure_cap(T *&p, size_t &cap, size_t need_bytes) {
+// Grows a staging buffer.  The zero fill is ordered on `st`, the stream every consumer of the buffer runs on
+// (a cudaMemset on the legacy stream would not be ordered with a cudaStreamNonBlocking stream).
+template <typename T> int ensure_cap(T *&p, size_t &cap, size_t need_bytes, cudaStream_t st) {
   if (need_bytes <= cap) return RT_OK;
-  if (p) cudaFree(p);
+  if (p) {
+    RT_CUDA(cudaStreamSynchronize(st)); // nothing in flight may still use the old block
+    cudaFree(p);
+  }
   p = nullptr;
   cap = 0;
   RT_CUDA(cudaMalloc(&p, need_bytes));
-  RT_CUDA(cudaMemset(p, 0, need_bytes));
+  RT_CUDA(cudaMemsetAsync(p, 0, need_bytes, st));
   cap = need_bytes;
   return RT_OK;
+}
+
+// Payload check of an adopted blob (it may come from a broadcast buffer or from the caller): every child reference,
+// leaf range and index table entry must stay inside its section, otherwise the render kernel would read out of
+// bounds.  One pass over the node records and the index tables, HBM-bound, once per scene.
+__global__ void validate_blob_kernel(SceneView v, int num_obj_tree, int *bad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  bool ok = true;
+  if (i < v.num_nodes) {
+    const NodeRec r = v.nodes[i];
+    const int limit = (v.obj_root >= 0 && i >= v.obj_root) ? num_obj_tree : v.num_tris;
+    const int ref[2] = {r.ref0, r.ref1}, cnt[2] = {r.cnt0, r.cnt1};
+    const bool empty[2] = {r.c0_half[0] < 0.0f, r.c1_half[0] < 0.0f};
+    for (int k = 0; k < 2; ++k) {
+      if (empty[k]) continue;
+      if (cnt[k] < 0 || ref[k] < 0) ok = false;
+      else if (cnt[k] == 0) ok = ok && ref[k] < v.num_nodes;
+      else ok = ok && (long long)ref[k] + cnt[k] <= limit;
+    }
+  }
+  if (i < v.num_nodes4) {
+    const Node4Rec r = v.nodes4[i];
+    const int limit = i >= v.num_nodes4_tri ? num_obj_tree : v.num_tris;
+    for (int k = 0; k < 4; ++k) {
+      if (r.ref[k] == -1 && r.cnt[k] == 0) continue; // empty slot
+      if (r.cnt[k] < 0 || r.ref[k] < 0) ok = false;
+      else if (r.cnt[k] == 0) ok = ok && r.ref[k] < v.num_nodes4;
+      else ok = ok && (long long)r.ref[k] + r.cnt[k] <= limit;
+    }
+  }
+  if (i < v.num_tris) {
+    ok = ok && (unsigned)v.tri_id[i] < (unsigned)v.num_tris && (unsigned)v.tri_pos[i] < (unsigned)v.num_tris;
+    ok = ok && (unsigned)v.shade[i].mesh < (unsigned)v.num_meshes;
+  }
+  if (i < num_obj_tree) ok = ok && (unsigned)v.obj_order[i] < (unsigned)v.num_objects;
+  if (i < v.num_lin) ok = ok && (unsigned)v.lin_idx[i] < (unsigned)v.num_objects;
+  if (!ok) atomicExch(bad, 1);
 }
 
 int adopt_blob(rt_scene *s) {
@@ -122,6 +165,20 @@ int adopt_blob(rt_scene *s) {
   s->view.tri_pos = reinterpret_cast<const int32_t *>(b + h.off_tri_pos);
   s->view.q_base = h.q_base;
   s->view.root_max_x = h.root_max_x;
+  {
+    int *d_bad = nullptr, bad = 0;
+    RT_CUDA(cudaMalloc(&d_bad, sizeof(int)));
+    RT_CUDA(cudaMemset(d_bad, 0, sizeof(int)));
+    long long n = h.num_nodes;
+    if (h.num_nodes4 > n) n = h.num_nodes4;
+    if (h.num_tris > n) n = h.num_tris;
+    if (h.num_objects > n) n = h.num_objects;
+    if (n > 0) validate_blob_kernel<<<(unsigned)((n + 255) / 256), 256>>>(s->view, h.num_obj_tree, d_bad);
+    cudaError_t e = cudaMemcpy(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost);
+    cudaFree(d_bad);
+    if (e != cudaSuccess) { set_error(std::string("blob validation: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+    if (bad) { set_error("blob: a child reference, leaf range or index table entry lies outside its section"); return RT_ERR_BAD_SCENE; }
+  }
   // texture objects over the blob's texel section ("textures go through texture objects")
   std::vector<MeshRec> meshes(h.num_meshes);
   if (h.num_meshes)
@@ -232,6 +289,12 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   a.scratch_d = s->d_scratch_d;
   a.scratch_i = s->d_scratch_i;
   const bool count = (fp.flags & RT_FLAG_COUNTERS) != 0;
+  // The slot's counter and event pair may still belong to the launch kRing launches ago, possibly on another
+  // stream: order this launch behind it, so any number of frames may be in flight (launches f and f + kRing
+  // serialise; include/rt_b200.h).  RT_FLAG_COUNTERS launches share one counter block and are synchronous
+  // (fetch_counters), so they never overlap each other.
+  if (s->slot_used[slot]) RT_CUDA(cudaStreamWaitEvent(st, s->ev1[slot], 0));
+  s->slot_used[slot] = true;
   RT_CUDA(cudaMemsetAsync(a.work_counter, 0, 2 * sizeof(unsigned long long), st));
   if (count) RT_CUDA(cudaMemsetAsync(s->d_counters, 0, sizeof(unsigned long long) * C_COUNT, st));
 #ifdef RT_TAILPROBE
@@ -308,17 +371,13 @@ int rt_scene_create_from_blob(const void *blob, size_t bytes, int is_device, rt_
   if (bytes < sizeof(h)) { set_error("blob: too small"); return RT_ERR_INVALID_ARG; }
   if (is_device) RT_CUDA(cudaMemcpy(&h, blob, sizeof(h), cudaMemcpyDeviceToHost));
   else std::memcpy(&h, blob, sizeof(h));
-  {
-    // validate the section table (header only; the payload was produced by flatten_scene)
-    std::vector<unsigned char> hb(sizeof(h));
-    std::memcpy(hb.data(), &h, sizeof(h));
-    if (h.magic != kBlobMagic || h.version != kBlobVersion || h.total_bytes != bytes) {
-      set_error("blob: bad magic/version/size");
-      return RT_ERR_BAD_SCENE;
-    }
-  }
+  // section table: every offset/count inside `bytes` (the payload is checked on the device in adopt_blob)
+  st = check_blob_header(h, bytes, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  int device = 0;
+  RT_CUDA(cudaGetDevice(&device));
   rt_scene *s = new rt_scene();
-  RT_CUDA(cudaGetDevice(&s->device));
+  s->device = device;
   s->bytes = bytes;
   s->hdr = h;
   cudaError_t e = cudaMalloc(&s->d_blob, bytes);
@@ -452,22 +511,22 @@ int rt_render(rt_scene *s, const rt_camera *camera, const rt_vec4 *lights_pos, c
   std::memset(&fo, 0, sizeof(fo));
   const bool partial = fp.tile_world > 1 && !(fp.flags & RT_FLAG_NO_CLEAR);
   if (out->rgba8) {
-    st = ensure_cap(s->d_rgba8, s->cap_rgba8, npx * 4); if (st != RT_OK) return st;
+    st = ensure_cap(s->d_rgba8, s->cap_rgba8, npx * 4, stx); if (st != RT_OK) return st;
     fo.rgba8 = s->d_rgba8;
     if (partial) RT_CUDA(cudaMemsetAsync(s->d_rgba8, 0, npx * 4, stx));
   }
   if (out->pixels) {
-    st = ensure_cap(s->d_pixels, s->cap_pixels, npx * 32); if (st != RT_OK) return st;
+    st = ensure_cap(s->d_pixels, s->cap_pixels, npx * 32, stx); if (st != RT_OK) return st;
     fo.pixels = s->d_pixels;
     if (partial) RT_CUDA(cudaMemsetAsync(s->d_pixels, 0, npx * 32, stx));
   }
   if (out->hit_id) {
-    st = ensure_cap(s->d_ids, s->cap_ids, npx * 4); if (st != RT_OK) return st;
+    st = ensure_cap(s->d_ids, s->cap_ids, npx * 4, stx); if (st != RT_OK) return st;
     fo.hit_id = s->d_ids;
     if (partial) RT_CUDA(cudaMemsetAsync(s->d_ids, 0xff, npx * 4, stx));
   }
   if (out->hit_t) {
-    st = ensure_cap(s->d_t, s->cap_t, npx * 8); if (st != RT_OK) return st;
+    st = ensure_cap(s->d_t, s->cap_t, npx * 8, stx); if (st != RT_OK) return st;
     fo.hit_t = s->d_t;
     if (partial) RT_CUDA(cudaMemsetAsync(s->d_t, 0, npx * 8, stx));
   }
@@ -565,7 +624,7 @@ int rt_launch_compute_image(rt_vec4 *d_pixels, rt_vec4 *d_tmpPixels, rt_vec4 *h_
   if (st != RT_OK) return st;
   // pass 2: adaptive supersampling, subp = 4, threshold = 0.02 (mytracer_gpu.cu:83-105)
   RT_CUDA(cudaMemcpyAsync(d_tmpPixels, d_pixels, npx * sizeof(rt_vec4), cudaMemcpyDeviceToDevice, stx));
-  st = ensure_cap(s->d_list, s->cap_list, (npx + 1) * sizeof(int));
+  st = ensure_cap(s->d_list, s->cap_list, (npx + 1) * sizeof(int), stx);
   if (st != RT_OK) return st;
   int *d_count = s->d_list + npx;
   RT_CUDA(cudaMemsetAsync(d_count, 0, sizeof(int), stx));
@@ -587,6 +646,192 @@ int rt_launch_compute_image(rt_vec4 *d_pixels, rt_vec4 *d_tmpPixels, rt_vec4 *h_
   // copy to host (mytracer_gpu.cu:112)
   if (h_image) RT_CUDA(cudaMemcpyAsync(h_image, d_pixels, npx * sizeof(rt_vec4), cudaMemcpyDeviceToHost, stx));
   RT_CUDA(cudaStreamSynchronize(stx));
+  return RT_OK;
+}
+
+// ---- pipelined host-buffer frames (replaces the body of Raytracer::compute_image_cuda, mytracer.cpp:123-159,
+// for a host that renders a sequence of frames: copyLights :105-118, the launch, the D2H copy mytracer_gpu.cu:112) ----
+struct rt_frame_queue {
+  rt_scene *scene = nullptr;
+  int width = 0, height = 0, depth = 2, ctas_per_sm = 0, zero_copy = 0;
+  size_t flush_bytes = 0;
+  unsigned char *d_flush = nullptr;
+  struct Slot {
+    cudaStream_t compute = nullptr;
+    uint8_t *d_rgba8 = nullptr;
+    double *d_lights = nullptr;   // pos[4*cap] then col[4*cap]
+    double *h_lights = nullptr;   // pinned staging (the caller may reuse its arrays as soon as submit returns)
+    int lights_cap = 0;
+    cudaEvent_t kernel_done = nullptr;
+    long long ticket = -1;        // frame in this slot (-1: free)
+  };
+  std::vector<Slot> slots;
+  cudaStream_t copy = nullptr;    // D2H engine stream: the copy of frame f overlaps the kernel of frame f + 1
+  static constexpr int kTimeRing = 64;
+  cudaEvent_t done[kTimeRing] = {}; // completion (after the D2H copy) of ticket t lives in done[t % kTimeRing]
+  cudaEvent_t origin = nullptr;     // recorded before the first frame: zero of the completion timeline
+  long long submitted = 0, retired = 0;
+  double last_done_ms = 0.0;        // completion time of ticket retired - 1 on the queue's timeline
+  std::vector<double> done_ms;      // [ticket % 4096]
+};
+
+namespace {
+int retire_upto(rt_frame_queue *q, long long ticket) {
+  while (q->retired <= ticket) {
+    const long long t = q->retired;
+    cudaEvent_t ev = q->done[t % rt_frame_queue::kTimeRing];
+    RT_CUDA(cudaEventSynchronize(ev));
+    float ms = 0.0f;
+    RT_CUDA(cudaEventElapsedTime(&ms, t == 0 ? q->origin : q->done[(t - 1) % rt_frame_queue::kTimeRing], ev));
+    q->last_done_ms += (double)ms;
+    q->done_ms[t % 4096] = q->last_done_ms;
+    q->slots[t % q->depth].ticket = -1;
+    q->retired = t + 1;
+  }
+  return RT_OK;
+}
+} // namespace
+
+int rt_frame_queue_create(rt_scene *scene, int width, int height, const rt_frame_queue_opts *opts, rt_frame_queue **out) {
+  if (!scene || !out || width <= 0 || height <= 0) { set_error("rt_frame_queue_create: invalid argument"); return RT_ERR_INVALID_ARG; }
+  rt_frame_queue *q = new rt_frame_queue();
+  q->scene = scene; q->width = width; q->height = height;
+  if (opts) {
+    q->depth = opts->depth > 0 ? opts->depth : 2;
+    q->ctas_per_sm = opts->ctas_per_sm > 0 ? opts->ctas_per_sm : 0;
+    q->flush_bytes = opts->flush_bytes;
+    q->zero_copy = opts->zero_copy != 0;
+  }
+  // two frames of the timeline ring must never share an event while both are unretired
+  if (q->depth > rt_frame_queue::kTimeRing / 2) { delete q; set_error("rt_frame_queue_create: depth > 32"); return RT_ERR_LIMIT; }
+  q->done_ms.assign(4096, 0.0);
+  q->slots.resize(q->depth);
+  auto fail = [&](int st) { rt_frame_queue_destroy(q); return st; };
+#define RT_Q(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(e_)); \
+                        return fail(e_ == cudaErrorMemoryAllocation ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA); } } while (0)
+  RT_Q(cudaStreamCreateWithFlags(&q->copy, cudaStreamNonBlocking));
+  RT_Q(cudaEventCreate(&q->origin));
+  for (int k = 0; k < rt_frame_queue::kTimeRing; ++k) RT_Q(cudaEventCreate(&q->done[k]));
+  for (auto &sl : q->slots) {
+    RT_Q(cudaStreamCreateWithFlags(&sl.compute, cudaStreamNonBlocking));
+    RT_Q(cudaEventCreateWithFlags(&sl.kernel_done, cudaEventDisableTiming));
+    if (!q->zero_copy) RT_Q(cudaMalloc(&sl.d_rgba8, (size_t)width * height * 4));
+  }
+  if (q->flush_bytes) RT_Q(cudaMalloc(&q->d_flush, q->flush_bytes));
+#undef RT_Q
+  *out = q;
+  return RT_OK;
+}
+
+int rt_frame_submit(rt_frame_queue *q, const rt_camera *camera, const rt_vec4 *lights_pos, const rt_vec4 *lights_color,
+                    int num_lights, const rt_render_params *params, uint8_t *rgba8_host, long long *ticket) {
+  if (!q || !camera || !params || !rgba8_host) { set_error("rt_frame_submit: null argument"); return RT_ERR_INVALID_ARG; }
+  if (camera->width != q->width || camera->height != q->height) { set_error("rt_frame_submit: camera size differs from the queue's"); return RT_ERR_INVALID_ARG; }
+  if (num_lights > 0 && (!lights_pos || !lights_color)) { set_error("rt_frame_submit: null lights"); return RT_ERR_INVALID_ARG; }
+  const long long t = q->submitted;
+  rt_frame_queue::Slot &sl = q->slots[t % q->depth];
+  int st;
+  if (sl.ticket >= 0) { st = retire_upto(q, sl.ticket); if (st != RT_OK) return st; } // at most `depth` frames in flight
+  if (num_lights > sl.lights_cap) {
+    if (sl.d_lights) cudaFree(sl.d_lights);
+    if (sl.h_lights) cudaFreeHost(sl.h_lights);
+    sl.d_lights = nullptr; sl.h_lights = nullptr; sl.lights_cap = 0;
+    RT_CUDA(cudaMalloc(&sl.d_lights, sizeof(double) * 8 * num_lights));
+    RT_CUDA(cudaHostAlloc(&sl.h_lights, sizeof(double) * 8 * num_lights, cudaHostAllocDefault));
+    sl.lights_cap = num_lights;
+  }
+  if (t == 0) RT_CUDA(cudaEventRecord(q->origin, sl.compute));
+  if (q->d_flush) RT_CUDA(cudaMemsetAsync(q->d_flush, 1, q->flush_bytes, sl.compute)); // benchmark aid: evict L2
+  double *d_lcol = sl.d_lights + 4 * (size_t)sl.lights_cap;
+  if (num_lights > 0) {
+    std::memcpy(sl.h_lights, lights_pos, sizeof(double) * 4 * num_lights);
+    std::memcpy(sl.h_lights + 4 * (size_t)sl.lights_cap, lights_color, sizeof(double) * 4 * num_lights);
+    RT_CUDA(cudaMemcpyAsync(sl.d_lights, sl.h_lights, sizeof(double) * 8 * sl.lights_cap, cudaMemcpyHostToDevice, sl.compute));
+  }
+  rt_frame_out fo;
+  std::memset(&fo, 0, sizeof(fo));
+  if (q->zero_copy) {
+    // the kernel stores every finished pixel straight into the caller's pinned, mapped host frame (one frame
+    // shared by all ranks' processes in the multi-GPU case): no staging buffer, no copy pass
+    void *dptr = nullptr;
+    RT_CUDA(cudaHostGetDevicePointer(&dptr, rgba8_host, 0));
+    fo.rgba8 = static_cast<uint8_t *>(dptr);
+  } else {
+    fo.rgba8 = sl.d_rgba8;
+  }
+  const int saved = q->scene->ctas_per_sm;
+  q->scene->ctas_per_sm = q->ctas_per_sm;
+  st = rt_render_device(q->scene, camera, reinterpret_cast<const rt_vec4 *>(sl.d_lights), reinterpret_cast<const rt_vec4 *>(d_lcol),
+                        num_lights, params, &fo, sl.compute);
+  q->scene->ctas_per_sm = saved;
+  if (st != RT_OK) return st;
+  cudaEvent_t done = q->done[t % rt_frame_queue::kTimeRing];
+  if (q->zero_copy) {
+    RT_CUDA(cudaEventRecord(done, sl.compute));
+  } else {
+    RT_CUDA(cudaEventRecord(sl.kernel_done, sl.compute));
+    RT_CUDA(cudaStreamWaitEvent(q->copy, sl.kernel_done, 0));
+    RT_CUDA(cudaMemcpyAsync(rgba8_host, sl.d_rgba8, (size_t)q->width * q->height * 4, cudaMemcpyDeviceToHost, q->copy));
+    RT_CUDA(cudaEventRecord(done, q->copy));
+    RT_CUDA(cudaStreamWaitEvent(sl.compute, done, 0)); // the slot's next kernel must not overwrite d_rgba8 under the copy
+  }
+  sl.ticket = t;
+  q->submitted = t + 1;
+  if (ticket) *ticket = t;
+  return RT_OK;
+}
+
+int rt_frame_wait(rt_frame_queue *q, long long ticket, double *done_ms) {
+  if (!q || ticket < 0 || ticket >= q->submitted) { set_error("rt_frame_wait: unknown ticket"); return RT_ERR_INVALID_ARG; }
+  if (ticket + 4096 <= q->retired) { set_error("rt_frame_wait: ticket too old"); return RT_ERR_INVALID_ARG; }
+  int st = retire_upto(q, ticket);
+  if (st != RT_OK) return st;
+  if (done_ms) *done_ms = q->done_ms[ticket % 4096];
+  return RT_OK;
+}
+
+int rt_frame_queue_destroy(rt_frame_queue *q) {
+  if (!q) return RT_OK;
+  if (q->submitted > 0) retire_upto(q, q->submitted - 1);
+  for (auto &sl : q->slots) {
+    if (sl.compute) { cudaStreamSynchronize(sl.compute); cudaStreamDestroy(sl.compute); }
+    if (sl.kernel_done) cudaEventDestroy(sl.kernel_done);
+    if (sl.d_rgba8) cudaFree(sl.d_rgba8);
+    if (sl.d_lights) cudaFree(sl.d_lights);
+    if (sl.h_lights) cudaFreeHost(sl.h_lights);
+  }
+  if (q->copy) { cudaStreamSynchronize(q->copy); cudaStreamDestroy(q->copy); }
+  for (int k = 0; k < rt_frame_queue::kTimeRing; ++k) if (q->done[k]) cudaEventDestroy(q->done[k]);
+  if (q->origin) cudaEventDestroy(q->origin);
+  if (q->d_flush) cudaFree(q->d_flush);
+  delete q;
+  return RT_OK;
+}
+
+// ---- pinned / mapped host memory for frame buffers --------------------------------------------------------
+int rt_host_alloc(size_t bytes, void **p) {
+  if (!p || bytes == 0) { set_error("rt_host_alloc: bad argument"); return RT_ERR_INVALID_ARG; }
+  std::string err;
+  int st = ensure_device(err);
+  if (st != RT_OK) { set_error(err); return st; }
+  RT_CUDA(cudaHostAlloc(p, bytes, cudaHostAllocPortable | cudaHostAllocMapped));
+  return RT_OK;
+}
+int rt_host_free(void *p) {
+  if (p) RT_CUDA(cudaFreeHost(p));
+  return RT_OK;
+}
+int rt_host_register(void *p, size_t bytes, void **dptr) {
+  if (!p || bytes == 0) { set_error("rt_host_register: bad argument"); return RT_ERR_INVALID_ARG; }
+  std::string err;
+  int st = ensure_device(err);
+  if (st != RT_OK) { set_error(err); return st; }
+  RT_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
+  if (dptr) RT_CUDA(cudaHostGetDevicePointer(dptr, p, 0));
+  return RT_OK;
+}
+int rt_host_unregister(void *p) {
+  if (p) RT_CUDA(cudaHostUnregister(p));
   return RT_OK;
 }
 

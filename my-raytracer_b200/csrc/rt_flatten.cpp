@@ -575,12 +575,18 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   return RT_OK;
 }
 
-int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
-  if (!blob || bytes < sizeof(BlobHeader)) { err = "blob: too small"; return RT_ERR_INVALID_ARG; }
-  BlobHeader h;
-  std::memcpy(&h, blob, sizeof(h));
+int check_blob_header(const BlobHeader &h, size_t bytes, std::string &err) {
   if (h.magic != kBlobMagic || h.version != kBlobVersion) { err = "blob: bad magic/version"; return RT_ERR_BAD_SCENE; }
   if (h.total_bytes != bytes) { err = "blob: size mismatch"; return RT_ERR_BAD_SCENE; }
+  const bool counts_ok = h.num_nodes >= 0 && h.num_tris >= 0 && h.num_meshes >= 0 && h.num_objects >= 0 &&
+                         h.num_nodes4 >= 0 && h.num_nodes_q >= 0 && h.q_base >= 0 && h.num_nodes_obj >= 0 &&
+                         h.num_obj_tree >= 0 && h.num_lin >= 0 && h.num_nodes4_tri >= 0 && h.num_texels <= bytes / 16;
+  if (!counts_ok) { err = "blob: negative record count"; return RT_ERR_BAD_SCENE; }
+  // every section: inside the blob, aligned for its record type, and in the flattener's order (no overlap)
+  const uint64_t offs[] = {h.off_nodes, h.off_filter, h.off_exact, h.off_shade, h.off_meshes, h.off_objects, h.off_texels,
+                           h.off_maxx, h.off_tri_id, h.off_tri_pos, h.off_objfilt, h.off_obj_order, h.off_lin_idx, h.off_nodes4};
+  for (uint64_t o : offs)
+    if (o < sizeof(BlobHeader) || o > bytes || o % 32 != 0) { err = "blob: section offset outside the blob or misaligned"; return RT_ERR_BAD_SCENE; }
   const bool ok = h.off_nodes + (size_t)h.num_nodes * sizeof(NodeRec) <= h.off_filter &&
                   h.off_filter + (size_t)h.num_tris * sizeof(TriFilter) <= h.off_exact &&
                   h.off_exact + (size_t)h.num_tris * sizeof(TriExact) <= h.off_shade &&
@@ -594,14 +600,21 @@ int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
                   h.off_objfilt + (size_t)h.num_objects * sizeof(ObjFilter) <= h.off_obj_order &&
                   h.off_obj_order + (size_t)h.num_obj_tree * sizeof(int32_t) <= h.off_lin_idx &&
                   h.off_lin_idx + (size_t)h.num_lin * sizeof(int32_t) <= h.off_nodes4 &&
-                  h.num_nodes4 >= 0 && h.off_nodes4 % 32 == 0 && h.num_nodes4_tri >= 0 && h.num_nodes4_tri <= h.num_nodes4 &&
+                  h.num_nodes4_tri <= h.num_nodes4 &&
                   h.obj_root4 >= -1 && h.obj_root4 < (h.num_nodes4 > 0 ? h.num_nodes4 : 1) &&
                   h.off_nodes4 + (size_t)h.num_nodes4 * sizeof(Node4Rec) <= h.total_bytes &&
-                  h.num_nodes_obj >= 0 && h.num_obj_tree >= 0 && h.num_lin >= 0 && h.num_obj_tree + h.num_lin == h.num_objects &&
+                  h.num_obj_tree + h.num_lin == h.num_objects &&
                   (h.obj_root < 0 ? h.num_nodes_obj == 0 : h.obj_root == h.q_base + h.num_nodes_q) &&
-                  h.q_base >= 0 && h.num_nodes_q >= 0 && (size_t)h.q_base + (size_t)h.num_nodes_q + (size_t)h.num_nodes_obj == (size_t)h.num_nodes;
+                  (size_t)h.q_base + (size_t)h.num_nodes_q + (size_t)h.num_nodes_obj == (size_t)h.num_nodes;
   if (!ok) { err = "blob: section table inconsistent"; return RT_ERR_BAD_SCENE; }
   return RT_OK;
+}
+
+int check_blob(const unsigned char *blob, size_t bytes, std::string &err) {
+  if (!blob || bytes < sizeof(BlobHeader)) { err = "blob: too small"; return RT_ERR_INVALID_ARG; }
+  BlobHeader h;
+  std::memcpy(&h, blob, sizeof(h));
+  return check_blob_header(h, bytes, err);
 }
 
 SceneView view_of_blob(const unsigned char *blob) {

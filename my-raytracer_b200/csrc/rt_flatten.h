@@ -14,6 +14,8 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
 
 // Validates a blob received from another rank (magic, version, section bounds).
 int check_blob(const unsigned char *blob, size_t bytes, std::string &err);
+// The same on a header already copied out of the blob (host or device resident).
+int check_blob_header(const BlobHeader &h, size_t bytes, std::string &err);
 
 // Host-side view of a blob (pointers into `blob`); tex_objs is left null.
 SceneView view_of_blob(const unsigned char *blob);

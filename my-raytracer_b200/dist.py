@@ -14,15 +14,17 @@ import torch
 import torch.distributed as dist
 
 
-def broadcast_blob(blob: bytes | None, device, src: int = 0) -> torch.Tensor:
-    """Rank `src` passes the exported blob bytes; every rank returns a uint8 tensor on `device`."""
+def broadcast_blob(blob, device, src: int = 0) -> torch.Tensor:
+    """Rank `src` passes the flattened scene — host bytes, or a uint8 tensor already on `device` (a view of the
+    resident blob, `wrap_device_ptr(*scene.blob_device())`: then the broadcast reads HBM directly, no host
+    round trip); every rank returns a uint8 tensor on `device`."""
     rank = dist.get_rank()
     n = torch.zeros(1, dtype=torch.int64, device=device)
     if rank == src:
-        n[0] = len(blob)
+        n[0] = blob.numel() if isinstance(blob, torch.Tensor) else len(blob)
     dist.broadcast(n, src)
     if rank == src:
-        t = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(device)
+        t = blob if isinstance(blob, torch.Tensor) else torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(device)
     else:
         t = torch.empty(int(n.item()), dtype=torch.uint8, device=device)
     dist.broadcast(t, src)
@@ -86,6 +88,77 @@ def dyn_split(width: int, height: int, world: int, fraction: float = 0.15):
     return dyn_tiles, 8
 
 
+class SharedHostFrames:
+    """One block of host memory that every rank's process maps (a file in /dev/shm: POSIX shared memory),
+    registered with the CUDA driver in each process (rt_host_register: pinned + device-mapped).  The end-to-end
+    multi-GPU frame lands here: every rank's render kernel stores the pixels it finishes straight into the ONE host
+    frame over its own PCIe link, so no rank funnels the whole frame through a single host link."""
+
+    def __init__(self, lib, nbytes, rank, world, device, register=True):
+        """register=False (CPU tests): the shared mapping only, no CUDA registration."""
+        import ctypes as C
+        import mmap
+        import os
+        from . import capi
+        self.lib, self.capi, self.nbytes, self.rank = lib, capi, int(nbytes), rank
+        name = [None]
+        if rank == 0:
+            name[0] = "/dev/shm/rt_b200_frames_%d_%08x" % (os.getpid(), int.from_bytes(os.urandom(4), "little"))
+            fd = os.open(name[0], os.O_CREAT | os.O_EXCL | os.O_RDWR, 0o600)
+            os.ftruncate(fd, self.nbytes)
+        if world > 1:
+            dist.broadcast_object_list(name, 0, device=device)
+        if rank != 0:
+            fd = os.open(name[0], os.O_RDWR)
+        self.path = name[0]
+        self.map = mmap.mmap(fd, self.nbytes)
+        os.close(fd)
+        self._anchor = (C.c_char * self.nbytes).from_buffer(self.map)
+        self.host_ptr = C.addressof(self._anchor)
+        self.registered = bool(register)
+        self.dev_ptr = None
+        if register:
+            d = C.c_void_p()
+            capi.check(lib.rt_host_register(C.c_void_p(self.host_ptr), self.nbytes, C.byref(d)), lib)
+            self.dev_ptr = d.value
+        if world > 1:
+            dist.barrier()                 # every rank has the file open and registered ...
+        if rank == 0:
+            os.unlink(self.path)           # ... so the name can go; the memory lives as long as a mapping does
+
+    def numpy(self):
+        import numpy as np
+        return np.frombuffer(self.map, dtype=np.uint8)
+
+    def close(self):
+        if self.map is not None:
+            if self.registered:
+                self.lib.rt_host_unregister(self.host_ptr)
+            self._anchor = None
+            try:
+                self.map.close()
+            except BufferError:
+                pass
+            self.map = None
+
+
+class FrameInputs:
+    """What a rank that did not build the scene needs to submit frames: camera, lights, render parameters
+    (HostScene minus the meshes; used for large scenes that only rank 0 assembles)."""
+
+    def __init__(self, desc, lib):
+        import numpy as np
+        from . import scene as _scene
+        self.desc, self.lib = desc, lib
+        self.camera = _scene.look_at(desc.camera, lib)
+        self.lights_pos = _scene._vec4_array([l[0] for l in desc.lights]) if desc.lights else np.zeros((0, 4))
+        self.lights_color = _scene._vec4_array([l[1] for l in desc.lights]) if desc.lights else np.zeros((0, 4))
+
+    def params(self, *a, **kw):
+        from . import scene as _scene
+        return _scene.HostScene.params(self, *a, **kw)
+
+
 class FramePipeline:
     """One frame = one render-kernel launch per rank (north star (c)):
 
@@ -103,7 +176,11 @@ class FramePipeline:
     """
 
     def __init__(self, lib, scene_handle, host_scene, device, width, height, depth=2, ring=4, tile_chunk=None,
-                 dyn_fraction=0.15, flush_bytes=0, ctas_per_sm=0):
+                 dyn_fraction=0.15, flush_bytes=0, ctas_per_sm=0, flush_mode="inline", spp_grid=1, shared_host=None):
+        """flush_mode: "inline" = the L2-evicting fill runs on the frame's own stream ahead of its kernel; "side" = one
+        fill per frame on a stream of its own, paced by the frames (frame f + depth waits for fill f) but not
+        serialised ahead of the kernel; "off".  shared_host: SharedHostFrames for host_io at world > 1 (zero-copy
+        stores into ONE host frame); None = rank 0 copies the gathered device frame to pinned memory."""
         import ctypes as C
         from . import capi
         self.C, self.capi, self.lib = C, capi, lib
@@ -111,7 +188,10 @@ class FramePipeline:
         self.W, self.H = width, height
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
-        self.depth, self.ring = max(1, depth), max(ring, depth + 1)
+        self.depth, self.ring = max(1, min(depth, 8)), max(ring, min(depth, 8) + 1)   # rt_b200.h: launch ring of 8
+        self.flush_mode = flush_mode if flush_bytes else "off"
+        self.spp_grid = spp_grid
+        self.shared_host = shared_host
         nb = width * height * 4
         self.frame_bytes = nb
         self._own = []
@@ -154,10 +234,14 @@ class FramePipeline:
         self.h_frames = [torch.zeros(nb, dtype=torch.uint8).pin_memory() for _ in range(self.ring)] if self.rank == 0 else None
         self.params = []
         for s in range(self.ring):
-            self.params.append(host_scene.params(tile=self.tile, flags=capi.RT_FLAG_NO_CLEAR,
+            self.params.append(host_scene.params(spp_grid=spp_grid, tile=self.tile, flags=capi.RT_FLAG_NO_CLEAR,
                                                  dyn=(self.dyn_tiles, self.dyn_chunk,
                                                       (self.ctr_ptr + 64 * s) if self.dyn_tiles else None)))
         self.submitted = 0
+        self.done_events = []            # completion event of every submitted frame (timing enabled)
+        self.flush_stream = torch.cuda.Stream(device=device) if self.flush_mode == "side" else None
+        self.flush_done = {}
+        self.kernel_done = {}
         # ctas_per_sm > 0: every frame's persistent grid takes only that many CTA slots per SM, so the frames in
         # flight run side by side (rt_scene_set_launch_width)
         self.ctas_per_sm = int(ctas_per_sm)
@@ -174,24 +258,44 @@ class FramePipeline:
         gate = f - self.ring + 1
         if gate >= 0:
             cs.wait_event(self.comm_done.pop(gate))
+        if self.flush_mode == "side":
+            # one L2-evicting fill per frame on its own stream, paced by the frames: it starts once the previous
+            # frame's kernel is done and frame f + depth waits for it, but it is not serialised ahead of frame f
+            prev = self.kernel_done.pop(f - 1, None)
+            if prev is not None:
+                self.flush_stream.wait_event(prev)
+            with torch.cuda.stream(self.flush_stream):
+                self.flush.fill_(1)
+                fe = torch.cuda.Event()
+                fe.record(self.flush_stream)
+            self.flush_done[f] = fe
+            old = self.flush_done.pop(f - self.depth, None)
+            if old is not None:
+                cs.wait_event(old)
+        zero_copy = host_io and self.shared_host is not None
         with torch.cuda.stream(cs):
-            if self.flush is not None:
+            if self.flush_mode == "inline":
                 self.flush.fill_(1)                      # evict the scene from L2 between timed frames
             if host_io:
                 self.d_lpos.copy_(self.h_lpos, non_blocking=True)   # copyLights (mytracer.cpp:105-118)
                 self.d_lcol.copy_(self.h_lcol, non_blocking=True)
-            fo = capi.FrameOut(self.fb_ptr + slot * self.frame_bytes, None, None, None)
+            # finished pixels go to rank 0's device frame (peer stores over NVLink) or, end to end at N > 1, straight
+            # into the host frame all ranks share (mapped pinned memory, each rank over its own PCIe link)
+            base = self.shared_host.dev_ptr if zero_copy else self.fb_ptr
+            fo = capi.FrameOut(base + slot * self.frame_bytes, None, None, None)
             capi.check(lib.rt_render_device(self.scene, C.byref(self.host.camera), self.d_lpos.data_ptr(),
                                             self.d_lcol.data_ptr(), self.nl, C.byref(self.params[slot]), C.byref(fo),
                                             C.c_void_p(cs.cuda_stream)), lib)
             done = torch.cuda.Event()
             done.record(cs)
+        if self.flush_mode == "side":
+            self.kernel_done[f] = done
         self.comm.wait_event(done)
         with torch.cuda.stream(self.comm):
             if self.world > 1:
                 dist.all_reduce(self.signal)             # completion signal + flow control (4 bytes)
             if self.rank == 0:
-                if host_io:                              # consumer: the finished frame goes to the host
+                if host_io and not zero_copy:            # consumer: the finished frame goes to the host
                     self.h_frames[slot].copy_(self.fb_view[slot * self.frame_bytes:(slot + 1) * self.frame_bytes],
                                               non_blocking=True)
                 if self.dyn_tiles:
@@ -199,6 +303,7 @@ class FramePipeline:
             ev = torch.cuda.Event(enable_timing=True)
             ev.record(self.comm)
         self.comm_done[f] = ev
+        self.done_events.append(ev)
         self.last_event = ev
         self.submitted += 1
         return slot
@@ -207,9 +312,19 @@ class FramePipeline:
         """Rank 0: uint8 view (H, W, 4) of the frame in ring slot `slot` (valid after its signal completed)."""
         return self.fb_view[slot * self.frame_bytes:(slot + 1) * self.frame_bytes].view(self.H, self.W, 4)
 
+    def host_frame(self, slot):
+        """Rank 0: numpy uint8 view (H, W, 4) of the end-to-end frame in ring slot `slot`."""
+        if self.shared_host is not None:
+            a = self.shared_host.numpy()[slot * self.frame_bytes:(slot + 1) * self.frame_bytes]
+        else:
+            a = self.h_frames[slot].numpy()
+        return a.reshape(self.H, self.W, 4)
+
     def drain(self):
         for s in self.compute:
             s.synchronize()
+        if self.flush_stream is not None:
+            self.flush_stream.synchronize()
         self.comm.synchronize()
 
     def close(self):

@@ -24,7 +24,9 @@ def _worker(rank, world, port, q):
     lib = rt.load_library()
     host = rt.HostScene(rt.scenes.mixed_small(width=90, height=50), lib)      # every rank can describe the scene
     blob = sim.flatten(host) if rank == 0 else None                            # ...but only rank 0 flattens it
-    t = rdist.broadcast_blob(blob, "cpu")
+    # rank 0 hands the broadcast a tensor view of the resident blob (on the GPU: a view of HBM, no host round trip)
+    src = torch.frombuffer(bytearray(blob), dtype=torch.uint8) if rank == 0 else None
+    t = rdist.broadcast_blob(src, "cpu")
     blob_r = bytes(t.numpy())
     # static chunked interleave + the dynamic tail (host build: pool chunk q goes to rank q % world)
     dyn_tiles, dyn_chunk = rdist.dyn_split(90, 50, world, 0.3)
@@ -33,8 +35,17 @@ def _worker(rank, world, port, q):
     local = torch.from_numpy(part["rgba8"].copy())
     full = rdist.gather_frame(local, torch.empty_like(local))
     ms = rdist.max_over_ranks(float(rank + 1), "cpu")
+    # the end-to-end frame of the multi-GPU path: ONE host block every rank's process maps (POSIX shm); each rank
+    # stores the pixels it rendered (on the GPU: its kernel does, through the registered mapping)
+    shm = rdist.SharedHostFrames(lib, 90 * 50 * 4, rank, world, "cpu", register=False)
+    mine = part["rgba8"][..., 3] == 255
+    shm.numpy().reshape(50, 90, 4)[mine] = part["rgba8"][mine]
+    dist.barrier()
+    shared_frame = shm.numpy().reshape(50, 90, 4).copy()
+    dist.barrier()
+    shm.close()
     if rank == 0:
-        q.put((full.numpy().copy(), len(blob_r), ms))
+        q.put((full.numpy().copy(), len(blob_r), ms, shared_frame))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -46,7 +57,7 @@ def test_two_rank_frame_equals_single_rank():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    full, nbytes, ms = q.get(timeout=240)
+    full, nbytes, ms, shared_frame = q.get(timeout=240)
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -59,3 +70,4 @@ def test_two_rank_frame_equals_single_rank():
     ref = sim.render(host, blob)
     assert nbytes == len(blob) and ms == 2.0
     assert np.array_equal(full, ref["rgba8"])
+    assert np.array_equal(shared_frame, ref["rgba8"])

@@ -18,7 +18,7 @@ def test_cabi_exports_every_declared_symbol(rt, lib):
     assert declared == set(capi.PROTOTYPES), declared ^ set(capi.PROTOTYPES)
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.rt_abi_version() == 4
+    assert lib.rt_abi_version() == 5
 
 
 def test_struct_layouts_match_reference_headers(rt):
@@ -324,3 +324,25 @@ def test_tile_sharding_partitions_the_image(rt, lib, sim):
             acc[mask] = part["rgba8"][mask]
         assert (seen == 1).all()
         assert np.array_equal(acc, full["rgba8"])
+
+
+def test_blob_header_mirror_and_frame_inputs(rt, lib, sim):
+    """blobfmt.BlobHeader == csrc/rt_types.h BlobHeader (240 bytes, same offsets): magic, version, byte count and an
+    ascending 512-byte-aligned section table on a blob the flattener made; FrameInputs (what a rank that did not build
+    the scene submits frames with) carries the same camera, lights and render parameters as the HostScene."""
+    from my_raytracer_b200 import blobfmt
+    from my_raytracer_b200 import dist as rdist
+    desc = rt.scenes.mixed_small(width=16, height=12)
+    host = rt.HostScene(desc, lib)
+    blob = sim.flatten(host)
+    h = blobfmt.header(blob)
+    assert C.sizeof(blobfmt.BlobHeader) == 240
+    assert h["magic"] == blobfmt.BLOB_MAGIC and h["version"] == blobfmt.BLOB_VERSION and h["total_bytes"] == len(blob)
+    offs = [h[k] for k in ("off_nodes", "off_filter", "off_exact", "off_shade", "off_meshes", "off_objects", "off_texels",
+                           "off_maxx", "off_tri_id", "off_tri_pos", "off_objfilt", "off_obj_order", "off_lin_idx", "off_nodes4")]
+    assert offs == sorted(offs) and all(o % 512 == 0 and o <= len(blob) for o in offs)
+    assert h["num_tris"] == host.num_triangles and h["num_objects"] == host.num_objects
+    fi = rdist.FrameInputs(desc, lib)
+    assert bytes(fi.camera) == bytes(host.camera)
+    assert np.array_equal(fi.lights_pos, host.lights_pos) and np.array_equal(fi.lights_color, host.lights_color)
+    assert bytes(fi.params(spp_grid=2, tile=(1, 4, 16))) == bytes(host.params(spp_grid=2, tile=(1, 4, 16)))

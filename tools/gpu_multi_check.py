@@ -30,13 +30,18 @@ def main():
     lib = rt.load_library()
     capi.check(lib.rt_init_device(local), lib)
     dist.init_process_group("nccl", device_id=dev, pg_options=dist.ProcessGroupNCCL.Options(is_high_priority_stream=True))
-    host = rt.HostScene(rt.scenes.office(width=W, height=H), lib)
-    blob = rt.DeviceScene(host).export_blob() if rank == 0 else None
-    t_blob = rdist.broadcast_blob(blob, dev)
-    scene = rt.DeviceScene(lib=lib, blob_device_ptr=t_blob.data_ptr(), blob_bytes=t_blob.numel())
+    desc = rt.scenes.office(width=W, height=H)
+    # only rank 0 assembles and flattens the scene; the others get the blob device-to-device and submit frames
+    # with the camera / lights / parameters alone
+    host = rt.HostScene(desc, lib) if rank == 0 else rdist.FrameInputs(desc, lib)
+    scene0 = rt.DeviceScene(host) if rank == 0 else None
+    t_blob = rdist.broadcast_blob(rdist.wrap_device_ptr(*scene0.blob_device(), device=dev) if rank == 0 else None, dev)
+    scene = scene0 if rank == 0 else rt.DeviceScene(lib=lib, blob_device_ptr=t_blob.data_ptr(), blob_bytes=t_blob.numel())
     ok = True
-    for depth, frac in ((2, 0.15), (1, 0.0), (3, 1.0)):
-        pipe = rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, dyn_fraction=frac)
+    shared = rdist.SharedHostFrames(lib, W * H * 4 * 5, rank, world, dev)
+    for depth, frac, mode, zc in ((2, 0.15, "inline", True), (1, 0.0, "off", False), (3, 1.0, "side", True)):
+        pipe = rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, dyn_fraction=frac,
+                                   flush_bytes=8 << 20, flush_mode=mode, shared_host=shared if zc else None)
         ref = None
         if rank == 0:
             ref = scene.render(host.camera, host.lights_pos, host.lights_color, host.params(), want=("rgba8",))["rgba8"]
@@ -46,14 +51,15 @@ def main():
             if rank == 0:
                 pipe.comm_done[f].synchronize()          # this frame's completion signal
                 got.append(pipe.frame(slot).cpu().numpy().copy())
-                if f % 2 == 1:
-                    got.append(pipe.h_frames[slot].numpy().reshape(H, W, 4).copy())
+                if f % 2 == 1:                          # the end-to-end frame: shared host block (zero copy) or rank 0's D2H
+                    got.append(pipe.host_frame(slot).copy())
         pipe.drain()
         if rank == 0:
             bad = [i for i, g in enumerate(got) if not np.array_equal(g, ref)]
-            print(f"world {world} depth {depth} dyn_fraction {frac}: {len(got)} frame copies checked, mismatching: {bad}", flush=True)
+            print(f"world {world} depth {depth} dyn_fraction {frac} flush {mode} zero_copy {zc}: {len(got)} frame copies checked, mismatching: {bad}", flush=True)
             ok = ok and not bad
         pipe.close()
+    shared.close()
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     dist.barrier()
