@@ -134,6 +134,12 @@ typedef struct rt_render_params {
 #define RT_FLAG_COUNTERS     2 /* run the instrumented kernel and fill rt_counters */
 #define RT_FLAG_NO_CLEAR     4 /* keep pixels of tiles owned by other ranks untouched */
 #define RT_FLAG_BINARY_NODES 8 /* A/B: ordinary rays walk the binary traversal tree instead of its 4-wide twin */
+#define RT_FLAG_WAVEFRONT   16 /* render the frame as a wavefront: TRACE / SHADE kernel pairs per bounce exchanging rays
+                                  through path-state columns in HBM (same arithmetic, bit-identical frame) instead of
+                                  the one persistent kernel; frames the wavefront does not cover (pixel lists, dynamic
+                                  tile queue, RT_FLAG_COUNTERS, > 30 lights) fall back to the persistent kernel.
+                                  RT_B200_PIPELINE=wavefront in the environment selects it for every frame. */
+#define RT_FLAG_MEGAKERNEL  32 /* always the one persistent kernel (overrides RT_B200_PIPELINE) */
 
 /* Output buffers; any pointer may be NULL.  All are W*H entries, index y*W + x
  * (mytracer_gpu.cu:158). */
@@ -280,6 +286,9 @@ int rt_get_counters(const rt_scene *scene, rt_counters *out);
 /* CUDA-event time of the last rt_render / rt_render_device kernel on this scene (ms);
  * synchronises on the end event. */
 int rt_last_kernel_ms(const rt_scene *scene, float *ms);
+/* Which pipeline the last frame of this scene ran on: 0 = the persistent kernel, 1 = the wavefront (RT_FLAG_WAVEFRONT
+ * asks for it; frames it does not cover fall back). */
+int rt_last_pipeline(const rt_scene *scene, int *pipeline);
 
 /* Exact-signature semantics of launch_compute_image_device (mytracer_gpu.cu:44-113): renders
  * into d_pixels (device, vec4), runs the adaptive supersampling pass (subp 4, threshold 0.02,

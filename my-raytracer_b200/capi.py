@@ -16,6 +16,7 @@ RT_OK = 0
 RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_BAD_SCENE, RT_ERR_LIMIT, RT_ERR_OOM = 1, 2, 3, 4, 5, 6
 RT_SPHERE, RT_PLANE = 0, 1
 RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR, RT_FLAG_BINARY_NODES = 1, 2, 4, 8
+RT_FLAG_WAVEFRONT, RT_FLAG_MEGAKERNEL = 16, 32
 RT_SCENE_REFERENCE_TOPOLOGY = 1
 
 c_int_p = C.POINTER(C.c_int)
@@ -161,6 +162,7 @@ PROTOTYPES = {
     "rt_ipc_close": (C.c_int, [C.c_void_p]),
     "rt_get_counters": (C.c_int, [C.c_void_p, C.POINTER(Counters)]),
     "rt_last_kernel_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "rt_last_pipeline": (C.c_int, [C.c_void_p, c_int_p]),
     "rt_launch_compute_image": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Camera),
                                           C.c_void_p, C.c_void_p, C.c_int, Vec4_p, Vec4_p, C.c_int,
                                           C.POINTER(DataSoA), C.POINTER(BvhNodesSoA), C.POINTER(C.c_void_p)]),

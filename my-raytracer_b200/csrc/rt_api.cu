@@ -9,6 +9,7 @@
 #include "rt_flatten.h"
 #include "rt_frame.h"
 #include "rt_kernel.cuh"
+#include "rt_wavefront.cuh"
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -62,6 +63,15 @@ struct rt_scene {
   int *d_scratch_i = nullptr;
   int *d_list = nullptr; // supersampling pixel list
   size_t cap_list = 0;
+  // wavefront pipeline (rt_wavefront.cuh): path-state columns and launch control block per ring slot
+  struct WfSlot {
+    double *wd = nullptr; int *wi = nullptr; unsigned char *occl = nullptr;
+    unsigned long long *ctl = nullptr;   // [0, kWfCtlTasks): task counters, one per TRACE launch; then the pending[] array
+    long long cap_paths = 0; int cap_lights = 0;
+  } wf[kRing];
+  int grid_wf[4] = {0, 0, 0, 0};         // resident CTAs x SMs of wf_trace_kernel<cfg>, cfg = (K_OBJ ? 1 : 0) | (K_WIDE ? 2 : 0)
+  int wavefront_default = 0;             // RT_B200_PIPELINE=wavefront
+  int last_pipeline = 0;                 // what the last launch ran: 0 persistent megakernel, 1 wavefront
   int grid_plain = 0, grid_count = 0;
   int grid_wide = 0, grid_wide_count = 0; // K_WIDE kernels (scenes whose trees all have 4-wide twins)
   bool wide_ok = false;
@@ -250,6 +260,17 @@ int adopt_blob(rt_scene *s) {
     s->grid_wide = prop.multiProcessorCount * (occ2 > 0 ? occ2 : 1);
     s->grid_wide_count = prop.multiProcessorCount * (occ3 > 0 ? occ3 : 1);
   }
+  {
+    // persistent grid of the wavefront TRACE kernel variants
+    const void *kw[4] = {(const void *)wf_trace_kernel<0>, (const void *)wf_trace_kernel<K_OBJ>,
+                         (const void *)wf_trace_kernel<K_WIDE>, (const void *)wf_trace_kernel<K_WIDE | K_OBJ>};
+    for (int k = 0; k < 4; ++k) {
+      int occ = 0;
+      RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kw[k], kBlockThreads, 0));
+      s->grid_wf[k] = prop.multiProcessorCount * (occ > 0 ? occ : 1);
+    }
+    if (const char *e = std::getenv("RT_B200_PIPELINE")) s->wavefront_default = std::strcmp(e, "wavefront") == 0;
+  }
   s->sm_count = prop.multiProcessorCount;
   s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
   s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
@@ -272,9 +293,17 @@ int adopt_blob(rt_scene *s) {
   return RT_OK;
 }
 
+bool wavefront_ok(const rt_scene *s, const FrameParams &fp, const int *d_list, const int *d_list_count);
+int launch_wavefront(rt_scene *s, const FrameParams &fp, const double *d_lpos, const double *d_lcol, const FrameOut &out,
+                     cudaStream_t st);
+
 int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const double *d_lcol, const FrameOut &out,
            const int *d_list, int list_count, cudaStream_t st, const int *d_list_count = nullptr,
            unsigned long long *dyn_counter = nullptr) {
+  if (((fp.flags & RT_FLAG_WAVEFRONT) || s->wavefront_default) && !(fp.flags & RT_FLAG_MEGAKERNEL) &&
+      wavefront_ok(s, fp, d_list, d_list_count))
+    return launch_wavefront(s, fp, d_lpos, d_lcol, out, st);
+  s->last_pipeline = 0;
   KernelArgs a;
   a.sv = s->view; a.fp = fp;
   a.light_pos = d_lpos; a.light_col = d_lcol;
@@ -323,6 +352,80 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
     case K_WIDE | K_COUNT: render_kernel<K_WIDE | K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
     case K_WIDE | K_OBJ: render_kernel<K_WIDE | K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
     default: render_kernel<K_WIDE | K_OBJ | K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
+  }
+  RT_CUDA(cudaGetLastError());
+  RT_CUDA(cudaEventRecord(s->ev1[slot], st));
+  s->timed = true;
+  return RT_OK;
+}
+
+// ---- the frame as a wavefront (rt_wavefront.cuh): TRACE / SHADE launches per bounce on one stream ----------------
+constexpr int kWfCtlTasks = 32;     // task counters of one pass (max_depth + 2 TRACE launches)
+constexpr int kWfCtlWords = 64;     // 8-byte words of a slot's control block: task counters, then pending[]
+constexpr int kWfMaxDepth = kWfCtlTasks - 2;
+
+// Can this frame run as a wavefront?  (The persistent megakernel renders everything else.)
+bool wavefront_ok(const rt_scene *s, const FrameParams &fp, const int *d_list, const int *d_list_count) {
+  return !d_list && !d_list_count && !(fp.flags & RT_FLAG_COUNTERS) && fp.num_lights <= kWfMaxLights &&
+         fp.max_depth <= kWfMaxDepth && fp.static_tiles == fp.tiles_x * fp.tiles_y;
+}
+
+int launch_wavefront(rt_scene *s, const FrameParams &fp, const double *d_lpos, const double *d_lcol, const FrameOut &out,
+                     cudaStream_t st) {
+  const int slot = (int)(s->launch_seq++ % rt_scene::kRing);
+  s->last_slot = slot;
+  s->last_pipeline = 1;
+  if (s->slot_used[slot]) RT_CUDA(cudaStreamWaitEvent(st, s->ev1[slot], 0)); // the slot's path state is free again
+  s->slot_used[slot] = true;
+  Ctx hc;
+  hc.fp = fp; hc.pixel_list = nullptr; hc.list_count = 0;
+  const long long npaths = work_slots(hc);
+  rt_scene::WfSlot &ws = s->wf[slot];
+  const int nl = fp.num_lights > 0 ? fp.num_lights : 1;
+  if (npaths > ws.cap_paths || nl > ws.cap_lights) {
+    RT_CUDA(cudaStreamSynchronize(st));
+    if (ws.wd) cudaFree(ws.wd);
+    if (ws.wi) cudaFree(ws.wi);
+    if (ws.occl) cudaFree(ws.occl);
+    ws.wd = nullptr; ws.wi = nullptr; ws.occl = nullptr; ws.cap_paths = 0; ws.cap_lights = 0;
+    RT_CUDA(cudaMalloc(&ws.wd, sizeof(double) * WD_NUM * (size_t)npaths));
+    RT_CUDA(cudaMalloc(&ws.wi, sizeof(int) * WI_NUM * (size_t)npaths));
+    RT_CUDA(cudaMalloc(&ws.occl, (size_t)nl * (size_t)npaths));
+    if (!ws.ctl) RT_CUDA(cudaMalloc(&ws.ctl, sizeof(unsigned long long) * kWfCtlWords));
+    ws.cap_paths = npaths; ws.cap_lights = nl;
+  }
+  WfArgs a;
+  a.sv = s->view; a.fp = fp;
+  a.light_pos = d_lpos; a.light_col = d_lcol;
+  a.out = out;
+  a.w.wd = ws.wd; a.w.wi = ws.wi; a.w.occl = ws.occl; a.w.npaths = npaths;
+  a.pending = reinterpret_cast<unsigned int *>(ws.ctl + kWfCtlTasks);
+  a.counters = s->d_counters;
+  const bool wide = s->wide_ok && !(fp.flags & RT_FLAG_BINARY_NODES);
+  const bool obj = s->hdr.obj_root >= 0;
+  const int cfg = (obj ? 1 : 0) | (wide ? 2 : 0);
+  int grid = s->grid_wf[cfg];
+  if (s->ctas_per_sm > 0) {
+    // a share of the machine per frame in flight, in units of the megakernel's CTA slots (4 per SM)
+    const long long lim = (long long)grid * s->ctas_per_sm / 4;
+    if (lim >= s->sm_count && lim < grid) grid = (int)lim;
+  }
+  const unsigned sgrid = (unsigned)((npaths + kBlockThreads - 1) / kBlockThreads);
+  RT_CUDA(cudaEventRecord(s->ev0[slot], st));
+  const int s2 = fp.spp_grid * fp.spp_grid;
+  for (int sample = 0; sample < s2; ++sample) {
+    RT_CUDA(cudaMemsetAsync(ws.ctl, 0, sizeof(unsigned long long) * kWfCtlWords, st));
+    a.sample = sample;
+    for (int b = 0; b <= fp.max_depth + 1; ++b) {
+      a.bounce = b;
+      a.task_counter = ws.ctl + b;
+      switch (cfg) {
+        case 0: wf_trace_kernel<0><<<grid, kBlockThreads, 0, st>>>(a); wf_shade_kernel<0><<<sgrid, kBlockThreads, 0, st>>>(a); break;
+        case 1: wf_trace_kernel<K_OBJ><<<grid, kBlockThreads, 0, st>>>(a); wf_shade_kernel<K_OBJ><<<sgrid, kBlockThreads, 0, st>>>(a); break;
+        case 2: wf_trace_kernel<K_WIDE><<<grid, kBlockThreads, 0, st>>>(a); wf_shade_kernel<K_WIDE><<<sgrid, kBlockThreads, 0, st>>>(a); break;
+        default: wf_trace_kernel<K_WIDE | K_OBJ><<<grid, kBlockThreads, 0, st>>>(a); wf_shade_kernel<K_WIDE | K_OBJ><<<sgrid, kBlockThreads, 0, st>>>(a); break;
+      }
+    }
   }
   RT_CUDA(cudaGetLastError());
   RT_CUDA(cudaEventRecord(s->ev1[slot], st));
@@ -429,6 +532,7 @@ int rt_scene_destroy(rt_scene *s) {
   F(s->d_blob); F(s->d_tex); F(s->d_work); F(s->d_counters); F(s->d_lights);
   F(s->d_scratch_d); F(s->d_scratch_i); F(s->d_rgba8); F(s->d_pixels); F(s->d_ids); F(s->d_t); F(s->d_list);
   for (int k = 0; k < rt_scene::kRing; ++k) {
+    F(s->wf[k].wd); F(s->wf[k].wi); F(s->wf[k].occl); F(s->wf[k].ctl);
     if (s->ev0[k]) cudaEventDestroy(s->ev0[k]);
     if (s->ev1[k]) cudaEventDestroy(s->ev1[k]);
   }
@@ -581,6 +685,12 @@ int rt_ipc_close(void *dptr) {
 int rt_get_counters(const rt_scene *s, rt_counters *out) {
   if (!s || !out) { set_error("rt_get_counters: null argument"); return RT_ERR_INVALID_ARG; }
   *out = s->counters;
+  return RT_OK;
+}
+
+int rt_last_pipeline(const rt_scene *s, int *pipeline) {
+  if (!s || !pipeline) { set_error("rt_last_pipeline: null argument"); return RT_ERR_INVALID_ARG; }
+  *pipeline = s->last_pipeline;
   return RT_OK;
 }
 

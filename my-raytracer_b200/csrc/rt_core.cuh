@@ -501,7 +501,8 @@ template <int COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold
 // ---------------------------------------------------------------------------------------
 // path logic (cold: FP64, runs once per ray, not per node)
 // ---------------------------------------------------------------------------------------
-template <int COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const Cold<S> &C) {
+// Camera::primary_ray direction (unnormalised) of the lane's pixel and sub-pixel sample (CI_PX, CI_PY, CI_SAMPLE)
+template <int S> RT_HD D3 primary_dir(const Ctx &c, const Cold<S> &C) {
   const CameraRec &cam = c.fp.cam;
   double x = (double)C.i(CI_PX), y = (double)C.i(CI_PY);
   const int s = c.fp.spp_grid;
@@ -515,13 +516,16 @@ template <int COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const
     y = dadd(y, yo);
   }
   // Camera::primary_ray: Ray(eye, lower_left + x*x_dir + y*y_dir - eye)
-  const D3 eye = ld3(cam.eye);
-  const D3 dir = sub(add(add(ld3(cam.lower_left), scale(x, ld3(cam.x_dir))), scale(y, ld3(cam.y_dir))), eye);
+  return sub(add(add(ld3(cam.lower_left), scale(x, ld3(cam.x_dir))), scale(y, ld3(cam.y_dir))), ld3(cam.eye));
+}
+
+template <int COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const Cold<S> &C) {
+  const D3 dir = primary_dir(c, C);
   C.i(CI_DEPTH) = 0;
   C.d(CD_WEIGHT) = 1.0;
   C.set(CD_COL, mk(0.0, 0.0, 0.0));
   bump<COUNT>(c, C_RAY_PRIMARY);
-  start_ray<COUNT>(c, H, C, eye, dir, M_NEAREST, DBL_MAX);
+  start_ray<COUNT>(c, H, C, ld3(c.fp.cam.eye), dir, M_NEAREST, DBL_MAX);
 }
 
 template <int S> RT_HD void write_pixel(const Ctx &c, const Cold<S> &C) {

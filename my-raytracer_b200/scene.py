@@ -305,6 +305,12 @@ class DeviceScene:
             out["counters"] = c.as_dict()
         return out
 
+    def last_pipeline(self) -> str:
+        """Which pipeline the last frame ran on: "megakernel" (one persistent kernel) or "wavefront"."""
+        k = C.c_int()
+        check(self.lib.rt_last_pipeline(self.handle, C.byref(k)), self.lib)
+        return "wavefront" if k.value == 1 else "megakernel"
+
     def last_kernel_ms(self) -> float:
         ms = C.c_float()
         check(self.lib.rt_last_kernel_ms(self.handle, C.byref(ms)), self.lib)

@@ -5,7 +5,7 @@
 // it with the oracle before GPU minutes are spent.  It is NOT a product path: nothing in
 // my-raytracer_b200/ loads it, the C-ABI library never falls back to it, and bench.py never
 // times it.
-#include "../../my-raytracer_b200/csrc/rt_core.cuh"
+#include "../../my-raytracer_b200/csrc/rt_wavefront.cuh"
 #include "../../my-raytracer_b200/csrc/rt_flatten.h"
 #include "../../my-raytracer_b200/csrc/rt_frame.h"
 #include <cstdlib>
@@ -109,6 +109,73 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
     for (int k = 0; k < C_COUNT; ++k) total[k] += mine[k];
   }
   if (counters) for (int k = 0; k < C_COUNT; ++k) counters[k] = total[k];
+  return RT_OK;
+}
+
+// The same frame through the WAVEFRONT schedule (rt_wavefront.cuh): the stage functions the CUDA kernels call
+// (wf_ray_start / traverse / wf_ray_finish, wf_shade), one path at a time, in the launch order of rt_api.cu.
+int sim_render_wavefront(const unsigned char *blob, size_t bytes, const rt_camera *cam, const rt_vec4 *lpos,
+                         const rt_vec4 *lcol, int nlights, const rt_render_params *params, const rt_frame_out *out,
+                         unsigned long long *counters) {
+  using namespace rtb;
+  std::string err;
+  int st = check_blob(blob, bytes, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  Ctx c;
+  st = make_frame_params(cam, nlights, params, out, c.fp, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  if (nlights > kWfMaxLights || c.fp.static_tiles != c.fp.tiles_x * c.fp.tiles_y) { set_error("wavefront: unsupported frame"); return RT_ERR_LIMIT; }
+  c.sv = view_of_blob(blob);
+  c.light_pos = reinterpret_cast<const double *>(lpos);
+  c.light_col = reinterpret_cast<const double *>(lcol);
+  c.pixel_list = nullptr;
+  c.list_count = 0;
+  c.out.rgba8 = out->rgba8;
+  c.out.pixels = reinterpret_cast<double *>(out->pixels);
+  c.out.hit_id = out->hit_id;
+  c.out.hit_t = out->hit_t;
+  unsigned int cnt[C_COUNT] = {0};
+  c.cnt = cnt;
+  const long long np = work_slots(c);
+  std::vector<double> wd((size_t)WD_NUM * np, 0.0);
+  std::vector<int> wi((size_t)WI_NUM * np, 0);
+  std::vector<unsigned char> occl((size_t)(nlights > 0 ? nlights : 1) * np, 0);
+  WfState w{wd.data(), wi.data(), occl.data(), np};
+  const bool wide = wide_usable(c.sv) && !(c.fp.flags & RT_FLAG_BINARY_NODES);
+  StackEntry stk[kStackMax];
+  double tcold[CD_BEST_T + 1];
+  Cold<1> T; T.db = tcold; T.ib = nullptr;
+  auto trace = [&](int kind, int sample) {
+    for (long long p = 0; p < np; ++p) {
+      Hot H;
+      H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0;
+      bool has;
+      if (wide) {
+        has = wf_ray_start<K_COUNT | K_OBJ | K_WIDE>(c, w, p, kind, sample, H, T);
+        if (has && H.node != -1) traverse<K_COUNT | K_OBJ | K_WIDE>(c, H, T, stk);
+      } else {
+        has = wf_ray_start<K_COUNT | K_OBJ>(c, w, p, kind, sample, H, T);
+        if (has && H.node != -1) traverse<K_COUNT | K_OBJ>(c, H, T, stk);
+      }
+      if (has) wf_ray_finish(c, w, p, kind, H, T);
+    }
+  };
+  auto shade = [&]() {
+    long long more = 0;
+    for (long long p = 0; p < np; ++p) more += wf_shade<K_COUNT | K_OBJ | K_WIDE>(c, w, p) ? 1 : 0;
+    return more;
+  };
+  const int s2 = c.fp.spp_grid * c.fp.spp_grid;
+  for (int sample = 0; sample < s2; ++sample) {
+    trace(-1, sample);
+    long long more = shade();
+    for (int b = 1; b <= c.fp.max_depth + 1 && more; ++b) {
+      for (int k = 0; k <= nlights; ++k) trace(k, sample);
+      more = shade();
+    }
+    if (more) { set_error("wavefront: paths left after max_depth + 1 bounces"); return RT_ERR_LIMIT; }
+  }
+  if (counters) for (int k = 0; k < C_COUNT; ++k) counters[k] = cnt[k];
   return RT_OK;
 }
 

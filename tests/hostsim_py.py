@@ -38,7 +38,10 @@ def flatten(host, scene_flags=0):
     return out
 
 
-def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, camera=None, cost=False, dyn=(0, 0)):
+def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, camera=None, cost=False, dyn=(0, 0),
+           wavefront=False):
+    """wavefront: the frame through the wavefront schedule (rt_wavefront.cuh stage functions) instead of the
+    per-lane state machine of the persistent kernel."""
     from my_raytracer_b200 import capi
     L = lib()
     blob = blob if blob is not None else flatten(host)
@@ -57,8 +60,14 @@ def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, 
     cnt = (C.c_ulonglong * 16)()
     cost_n = np.zeros((H, W), np.uint32); cost_t = np.zeros((H, W), np.uint32)
     lp, lc = host.lights_pos, host.lights_color
-    st = L.sim_render(buf, len(blob), C.byref(cam), lp.ctypes.data, lc.ctypes.data, lp.shape[0], C.byref(p),
-                      C.byref(fo), cnt, 0, cost_n.ctypes.data if cost else None, cost_t.ctypes.data if cost else None)
+    if wavefront:
+        L.sim_render_wavefront.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                           C.c_void_p, C.c_void_p]
+        st = L.sim_render_wavefront(buf, len(blob), C.byref(cam), lp.ctypes.data, lc.ctypes.data, lp.shape[0], C.byref(p),
+                                    C.byref(fo), cnt)
+    else:
+        st = L.sim_render(buf, len(blob), C.byref(cam), lp.ctypes.data, lc.ctypes.data, lp.shape[0], C.byref(p),
+                          C.byref(fo), cnt, 0, cost_n.ctypes.data if cost else None, cost_t.ctypes.data if cost else None)
     if st != 0:
         raise RuntimeError("sim_render status %d: %s" % (st, L.sim_last_error().decode()))
     names = ("rays_primary", "rays_shadow", "rays_reflect", "box_tests", "tri_filter", "tri_exact", "object_tests",

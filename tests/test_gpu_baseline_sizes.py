@@ -94,7 +94,7 @@ def test_frame_queue_matches_the_synchronous_call(rt, lib, gpu):
         tickets = []
         for f in range(nframes):
             lights = lp2 if f % 3 == 1 else lp
-            arr = np.ascontiguousarray(lights)
+            arr = lights.copy()
             gpu.check(lib.rt_frame_submit(q, C.byref(host.camera), arr.ctypes.data_as(gpu.Vec4_p), lc.ctypes.data_as(gpu.Vec4_p),
                                           lp.shape[0], C.byref(p), C.c_void_p(hbuf.value + f * nb), C.byref(tick)), lib)
             arr[:] = 0.0                                     # the caller's arrays may be reused once submit returns
@@ -185,3 +185,33 @@ def test_corrupt_blobs_are_rejected(rt, lib, gpu):
     off = hdr["off_tri_id"]
     bad[off:off + 4] = (hdr["num_tris"] + 5).to_bytes(4, "little")
     assert adopt(bad) == gpu.RT_ERR_BAD_SCENE
+
+
+@pytest.mark.parametrize("name,kw,spp,tile", [
+    ("office", dict(width=642, height=363), 1, (0, 1, 1)),
+    ("office", dict(width=322, height=181), 1, (2, 3, 4)),             # a rank's tile share, pixels of other ranks untouched
+    ("mixed_small", dict(width=333, height=201, seed=9), 2, (0, 1, 1)),  # 2x2 sub-pixel grid: four passes over the same paths
+    ("scatter", dict(width=256, height=144, n_objects=300), 1, (0, 1, 1)),   # d.x == 0 rays
+    ("textured", dict(width=256, height=144, tex_size=256, slices=64, stacks=32), 1, (0, 1, 1)),
+    ("molecule", dict(width=200, height=200, n_spheres=300), 1, (0, 1, 1)),  # object tree
+    ("objtree", dict(width=192, height=144), 1, (0, 1, 1)),
+    ("rings", dict(width=210, height=150, nu=96, nv=24), 1, (0, 1, 1)),
+])
+def test_wavefront_pipeline_is_bit_identical_to_the_persistent_kernel(rt, lib, gpu, name, kw, spp, tile):
+    """RT_FLAG_WAVEFRONT (TRACE / SHADE kernel pairs per bounce, rt_wavefront.cuh) against the one persistent kernel:
+    the same frame bit for bit — 8-bit and FP64 pixels, primary hit ids and ray parameters — also on the binary nodes."""
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    dev = rt.DeviceScene(host)
+    args = (host.camera, host.lights_pos, host.lights_color)
+    want = ("rgba8", "pixels", "hit_id", "hit_t") if spp == 1 else ("rgba8", "pixels")
+    mega = dev.render(*args, host.params(spp_grid=spp, tile=tile, flags=gpu.RT_FLAG_MEGAKERNEL), want=want)
+    assert dev.last_pipeline() == "megakernel"
+    wave = dev.render(*args, host.params(spp_grid=spp, tile=tile, flags=gpu.RT_FLAG_WAVEFRONT), want=want)
+    assert dev.last_pipeline() == "wavefront"
+    wave_b = dev.render(*args, host.params(spp_grid=spp, tile=tile, flags=gpu.RT_FLAG_WAVEFRONT | gpu.RT_FLAG_BINARY_NODES), want=want)
+    for k in want:
+        assert np.array_equal(mega[k], wave[k]), k
+        assert np.array_equal(mega[k], wave_b[k]), k
+    # frames the wavefront does not cover fall back to the persistent kernel
+    dev.render(*args, host.params(spp_grid=spp, tile=tile, flags=gpu.RT_FLAG_WAVEFRONT | gpu.RT_FLAG_COUNTERS), want=("rgba8",))
+    assert dev.last_pipeline() == "megakernel"

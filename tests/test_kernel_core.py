@@ -315,3 +315,24 @@ def test_object_tree_keeps_list_order_semantics(rt, lib, sim, orc, oracle_kind):
     assert np.abs(tree["pixels"][..., :3] - ref["rgb"]).max() < 1e-9
     ids = set(np.unique(tree["hit_id"]).tolist())
     assert n + 1 in ids and n + 15 not in ids and n + 5 in ids and n + 16 not in ids   # the first of two equal hits is kept
+
+
+@pytest.mark.parametrize("name,kw,spp,tile", [
+    ("mixed_small", dict(width=120, height=90), 1, (0, 1, 1)),
+    ("mixed_small", dict(width=61, height=45), 2, (0, 1, 1)),          # sub-pixel samples = passes over the same paths
+    ("office", dict(width=160, height=90), 1, (1, 3, 4)),              # a rank's tile share
+    ("scatter", dict(width=96, height=54, n_objects=100), 1, (0, 1, 1)),   # d.x == 0 rays (reference tree, NaN quirk)
+    ("objtree", dict(width=96, height=72), 1, (0, 1, 1)),              # tree over analytic spheres + plane + triangles
+    ("textured", dict(width=96, height=54, tex_size=64, slices=32, stacks=16), 1, (0, 1, 1)),
+])
+def test_wavefront_schedule_renders_the_same_frame(rt, lib, sim, name, kw, spp, tile):
+    """The wavefront stage functions (rt_wavefront.cuh: wf_ray_start / traverse / wf_ray_finish, wf_shade — what the
+    TRACE and SHADE kernels call) in the launch order of rt_api.cu against the per-lane state machine of the persistent
+    kernel: bit-identical pixels (8-bit and FP64), hit ids, ray parameters and every counter (same rays, same tests)."""
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    blob = sim.flatten(host)
+    a = sim.render(host, blob, spp_grid=spp, tile=tile, want_ids=spp == 1)
+    b = sim.render(host, blob, spp_grid=spp, tile=tile, want_ids=spp == 1, wavefront=True)
+    for k in ("rgba8", "pixels", "hit_id", "hit_t"):
+        assert np.array_equal(a[k], b[k]), k
+    assert a["counters"] == b["counters"]
