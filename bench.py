@@ -75,6 +75,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--topology", default="sah", choices=["sah", "reference"],
                     help="tree ordinary rays walk: the library's SAH tree (default) or the reference's median-split topology")
+    ap.add_argument("--pipeline", default="megakernel", choices=["megakernel", "wavefront"],
+                    help="one persistent kernel per frame (default) or TRACE/SHADE kernel pairs per bounce (RT_FLAG_WAVEFRONT)")
     ap.add_argument("--no-ab", action="store_true", help="skip the A/B frames (other tree, binary nodes, flush modes)")
     a = ap.parse_args()
     a.workload = ALIASES.get(a.workload, a.workload)
@@ -311,7 +313,9 @@ def run_b200(args):
     # per SM each at 2-4 GPUs, 1 at 8: frames resident side by side, every warp renders 2-4x more tiles of its
     # frame) - profiles/r01_variants.md.  The 10 M-triangle frame is 20 ms of work: 2 frames in flight suffice.
     depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "2" if big else ("8" if world >= 2 else "4")))
-    dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", "0.15"))
+    # the wavefront shards tiles statically only (no cross-GPU dynamic tail)
+    dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", "0.15" if args.pipeline == "megakernel" else "0"))
+    pflags = capi.RT_FLAG_WAVEFRONT if args.pipeline == "wavefront" else capi.RT_FLAG_MEGAKERNEL
     FLUSH = int(os.environ.get("RT_FLUSH_MB", "160")) * 1024 * 1024             # > 126 MB L2 (env: experiments only)
     # 0 = full-width grids (one GPU); half-width at 2-4 GPUs; quarter-width at 8
     ctas = int(os.environ.get("RT_CTAS_PER_SM", "0" if (world == 1 or big) else ("2" if world < 8 else "1")))
@@ -324,7 +328,7 @@ def run_b200(args):
     def make_pipe(mode):
         return rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, tile_chunk=chunk,
                                    dyn_fraction=dyn_fraction, flush_bytes=FLUSH, ctas_per_sm=ctas, flush_mode=mode,
-                                   spp_grid=spp_grid, shared_host=shared)
+                                   spp_grid=spp_grid, shared_host=shared, flags=pflags)
     pipe = make_pipe(flush_mode)
     nl = pipe.nl
     stream = torch.cuda.current_stream()
@@ -380,6 +384,7 @@ def run_b200(args):
     total_ms, _ = steady(pipe, args.steps, host_io=False)
     ms_per_step = total_ms / args.steps
     value = rays_frame / (ms_per_step * 1e-3) / 1e6
+    pipeline_ran = scene.last_pipeline()
 
     # ---- e2e: HOST buffers inside the timed region ---------------------------------------------------------------
     e2e_frame_sha = None
@@ -392,7 +397,7 @@ def run_b200(args):
         nring = depth + 2
         capi.check(lib.rt_host_alloc(W * H * 4 * nring, C.byref(hbuf)), lib)
         lp = np.ascontiguousarray(host.lights_pos); lc = np.ascontiguousarray(host.lights_color)
-        qparams = host.params(spp_grid=spp_grid, flags=capi.RT_FLAG_NO_CLEAR)
+        qparams = host.params(spp_grid=spp_grid, flags=capi.RT_FLAG_NO_CLEAR | pflags)
         tick = C.c_longlong()
 
         def q_submit():
@@ -472,7 +477,7 @@ def run_b200(args):
                   "e2e_frame_equals_1gpu": e2e_frame_sha == sha1(np.ascontiguousarray(full["rgba8"]))}
 
     # ---- one frame at a time (latency): serial launches, CUDA events around the kernel ---------------------
-    sparams = host.params(spp_grid=spp_grid, tile=pipe.tile, flags=capi.RT_FLAG_NO_CLEAR)
+    sparams = host.params(spp_grid=spp_grid, tile=pipe.tile, flags=capi.RT_FLAG_NO_CLEAR | pflags)
     capi.check(lib.rt_scene_set_launch_width(scene.handle, 0), lib)     # one frame alone gets the whole machine
     kern_ms = []
     def evict():
@@ -548,13 +553,15 @@ def run_b200(args):
     t_fp32 = flops / (peak_tflops * 1e12)
     t_l2 = alg_bytes / (l2_bw * 1e9)
     traffic, traffic_file = ncu_traffic(args.workload)
-    standard = world == 1 and (W, H) == (wl["width"], wl["height"]) and args.topology == "sah" and wide and not args.objects
+    standard = (world == 1 and (W, H) == (wl["width"], wl["height"]) and args.topology == "sah" and wide and not args.objects
+                and pipeline_ran == "megakernel")
     roof = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
             # DRAM bytes per launch of this kernel on this workload, read from the committed `ncu --set full` summary
             # (dram__bytes_read.sum + dram__bytes_write.sum); only quoted for the configuration that capture was taken on
             "traffic": traffic if standard else None,
             "traffic_unit": "bytes per launch (ncu --set full, %s)" % traffic_file,
-            "kernel": "rtb::render_kernel<4>" if wide else "rtb::render_kernel<0>",
+            "kernel": ("rtb::wf_trace_kernel + rtb::wf_shade_kernel" if pipeline_ran == "wavefront" else
+                       "rtb::render_kernel<4>" if wide else "rtb::render_kernel<0>"),
             "timed_over": "flops of one frame / ms_per_step of the steady-state window (kernels of successive frames overlap, "
                           "so the per-launch duration is not the divisor; flush and launch gaps are inside)",
             "kernel_ms_single_frame": max(rank_ms), "kernel_ms_per_rank": rank_ms,
@@ -577,7 +584,8 @@ def run_b200(args):
             "metric": wl["metric"], "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32 filter + f64 decide/shade", "data": "synthetic",
-            "config": {"workload": args.workload, "triangles": info["num_triangles"], "bvh_nodes": info["num_nodes_ref"],
+            "config": {"workload": args.workload, "pipeline": pipeline_ran,
+                       "triangles": info["num_triangles"], "bvh_nodes": info["num_nodes_ref"],
                        "traversal_tree": ("reference median-split topology" if info["topology"] == 1 else
                                           "library-built SAH tree over the same triangles; reference tree kept for d.x == 0 rays"),
                        "traversal_records": info["num_nodes_traversal"],
@@ -605,7 +613,7 @@ def run_b200(args):
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(2 * nl * 32) * world, "d2h_bytes_per_step": W * H * 4,
                     "api": e2e_api, "sync": sync_e2e},
-            "gpu_launches": args.steps * world,
+            "gpu_launches": args.steps * world * (1 if pipeline_ran == "megakernel" else 2 * (desc.max_depth + 2) * spp_grid * spp_grid),
             "roofline": roof,
             "setup_ms": {"host_scene_build": host_ms, "flatten": info["flatten_ms"], "upload": info["upload_ms"],
                          "broadcast": bcast_ms, "blob_bytes": info["blob_bytes"],

@@ -791,9 +791,11 @@ int retire_upto(rt_frame_queue *q, long long ticket) {
     const long long t = q->retired;
     cudaEvent_t ev = q->done[t % rt_frame_queue::kTimeRing];
     RT_CUDA(cudaEventSynchronize(ev));
+    // completion time on the queue's timeline = CUDA-event time since the first submit (frames on different
+    // streams may complete out of ticket order, so each is measured against the origin, not against its predecessor)
     float ms = 0.0f;
-    RT_CUDA(cudaEventElapsedTime(&ms, t == 0 ? q->origin : q->done[(t - 1) % rt_frame_queue::kTimeRing], ev));
-    q->last_done_ms += (double)ms;
+    RT_CUDA(cudaEventElapsedTime(&ms, q->origin, ev));
+    q->last_done_ms = (double)ms;
     q->done_ms[t % 4096] = q->last_done_ms;
     q->slots[t % q->depth].ticket = -1;
     q->retired = t + 1;

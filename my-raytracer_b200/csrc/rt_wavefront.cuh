@@ -194,6 +194,9 @@ struct WfArgs {
   unsigned long long *counters;      // C_COUNT entries (K_COUNT builds)
 };
 
+#ifndef RT_WF_CLAIM
+#define RT_WF_CLAIM 8
+#endif
 #ifndef RT_WF_MIN_BLOCKS
 #define RT_WF_MIN_BLOCKS 5
 #endif
@@ -219,15 +222,23 @@ __global__ void __launch_bounds__(kBlockThreads, RT_WF_MIN_BLOCKS) wf_trace_kern
   StackEntry stk[kStackMax];
   const unsigned lane = threadIdx.x & 31u;
   const long long nbatch = (a.w.npaths + 31) / 32;
-  const long long ntasks = (a.bounce == 0 ? 1 : (long long)c.fp.num_lights + 1) * nbatch;
+  // After the first hits most paths of a frame may be dead (no mirror): a claim then covers RT_WF_CLAIM consecutive
+  // batches, so an empty stretch of the frame costs one atomic round trip per 256 paths instead of one per 32.  While
+  // more than a quarter of the paths are alive a claim is one batch: coarser claims cost 30 % on a dense stage (tail).
+  const bool sparse = a.bounce > 0 && (long long)a.pending[a.bounce - 1] * 4 < a.w.npaths;
+  const int per = sparse ? RT_WF_CLAIM : 1;
+  const long long claims_per_kind = (nbatch + per - 1) / per;
+  const long long nclaims = (a.bounce == 0 ? 1 : (long long)c.fp.num_lights + 1) * claims_per_kind;
   while (true) {
-    // warp-level work fetch: one atomicAdd claims the next 32 rays (one tile, one ray kind)
+    // warp-level work fetch: one atomicAdd claims the next batches of 32 rays (one tile each, one ray kind)
     unsigned long long t = 0;
     if (lane == 0) t = atomicAdd(a.task_counter, 1ull);
     t = __shfl_sync(kFullMask, t, 0);
-    if ((long long)t >= ntasks) break;
-    const int kind = a.bounce == 0 ? -1 : (int)((long long)t / nbatch);
-    const long long p = ((long long)t % nbatch) * 32 + lane;
+    if ((long long)t >= nclaims) break;
+    const int kind = a.bounce == 0 ? -1 : (int)((long long)t / claims_per_kind);
+    const long long b0 = ((long long)t % claims_per_kind) * per;
+    for (int j = 0; j < per && b0 + j < nbatch; ++j) {
+    const long long p = (b0 + j) * 32 + lane;
     Hot H;
     H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0;
     const bool has = p < a.w.npaths && wf_ray_start<COUNT>(c, a.w, p, kind, a.sample, H, T);
@@ -251,6 +262,7 @@ __global__ void __launch_bounds__(kBlockThreads, RT_WF_MIN_BLOCKS) wf_trace_kern
       if (!__any_sync(kFullMask, next_tree<COUNT>(c, H, T))) break;
     }
     if (has) wf_ray_finish(c, a.w, p, kind, H, T);
+    }
   }
   if (COUNT & K_COUNT) {
 #pragma unroll

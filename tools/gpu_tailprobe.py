@@ -10,9 +10,12 @@ rt = rtpkg.load()
 from my_raytracer_b200 import capi
 lib = rt.load_library()
 capi.check(lib.rt_init_device(0), lib)
-host = rt.HostScene(rt.scenes.office(), lib)
+name = os.environ.get("RT_SCENE", "office")                    # RT_SCENE=rings: BASELINE config 3 at 700x500
+desc = rt.scenes.REGISTRY[name]()
+host = rt.HostScene(desc, lib)
 dev = rt.DeviceScene(host)
-W, H = 1920, 1080
+W, H = int(desc.camera["width"]), int(desc.camera["height"])
+print("scene", name, W, H, flush=True)
 d_rgba = torch.zeros(H * W * 4, dtype=torch.uint8, device="cuda")
 d_lpos = torch.tensor(host.lights_pos, dtype=torch.float64, device="cuda")
 d_lcol = torch.tensor(host.lights_color, dtype=torch.float64, device="cuda")
