@@ -7,6 +7,11 @@
 // as is: one 64-byte NodeRec per interior node, children in the reference's left/right order,
 // leaves referencing the same [firstTriIdx_, firstTriIdx_+triCount_) ranges.
 #include "rt_flatten.h"
+#include <chrono>
+#include <mutex>
+#include <thread>
+#include <cstdio>
+#include <cstdlib>
 #include "rt_sah.h"
 #include <cmath>
 #include <cstring>
@@ -15,6 +20,26 @@
 
 namespace rtb {
 namespace {
+
+// Contiguous ranges of [0, n) on the host threads (the flattener's per-triangle passes and section copies are
+// independent per element; 10 M triangles are seconds of single-thread work otherwise).
+template <typename F> void parallel_ranges(size_t n, size_t min_chunk, F &&f) {
+  unsigned hw = std::thread::hardware_concurrency();
+  if (hw == 0) hw = 1;
+  if (hw > 32) hw = 32;
+  size_t parts = n / (min_chunk ? min_chunk : 1);
+  if (parts > hw) parts = hw;
+  if (parts <= 1) { f((size_t)0, n); return; }
+  std::vector<std::thread> th;
+  const size_t step = (n + parts - 1) / parts;
+  for (size_t b = 0; b < n; b += step) th.emplace_back([&f, b, step, n] { f(b, b + step < n ? b + step : n); });
+  for (auto &t : th) t.join();
+}
+void parallel_copy(void *dst, const void *src, size_t bytes) {
+  parallel_ranges(bytes, (size_t)8 << 20, [&](size_t b, size_t e) {
+    std::memcpy(static_cast<unsigned char *>(dst) + b, static_cast<const unsigned char *>(src) + b, e - b);
+  });
+}
 
 inline float round_down(double v) {
   float f = (float)v;
@@ -65,6 +90,15 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     }
   }
 
+  // RT_FLATTEN_TIMING=1: phase times on stderr (diagnostics)
+  const bool timing = std::getenv("RT_FLATTEN_TIMING") != nullptr;
+  auto t_last = std::chrono::steady_clock::now();
+  auto mark = [&](const char *what) {
+    if (!timing) return;
+    const auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[flatten] %-28s %9.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+    t_last = now;
+  };
   // ---- 1. walk the reference tree, number interior nodes in DFS pre-order -------------------
   std::vector<NodeRec> nodes;
   std::vector<NodeMaxX> maxx;
@@ -175,23 +209,33 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     }
   }
 
+  mark("reference tree walk");
   // ---- 2. per-triangle records -------------------------------------------------------------
   std::vector<TriFilter> filt(N);
   std::vector<TriExact> exact(N);
   std::vector<TriShade> shade(N);
   double extent = 0.0;
   const int nv = data ? data->tVertexCount_ : 0;
-  for (int i = 0; i < N; ++i) {
+  std::mutex err_mu;
+  long long err_at = -1;          // lowest failing triangle (deterministic message whatever the thread schedule)
+  int err_code = RT_OK;
+  auto fail_at = [&](int i, int code, const std::string &msg) {
+    std::lock_guard<std::mutex> g(err_mu);
+    if (err_at < 0 || i < err_at) { err_at = i; err_code = code; err = msg; }
+  };
+  parallel_ranges((size_t)N, 1 << 16, [&](size_t i_begin, size_t i_end) {
+  double extent_local = 0.0;
+  for (int i = (int)i_begin; i < (int)i_end; ++i) {
     const int v0 = data->vertexIdx_[3 * i], v1 = data->vertexIdx_[3 * i + 1], v2 = data->vertexIdx_[3 * i + 2];
     if (v0 < 0 || v1 < 0 || v2 < 0 || v0 >= nv || v1 >= nv || v2 >= nv) {
-      err = "flatten: vertex index out of range in triangle " + std::to_string(i);
-      return RT_ERR_BAD_SCENE;
+      fail_at(i, RT_ERR_BAD_SCENE, "flatten: vertex index out of range in triangle " + std::to_string(i));
+      break;
     }
     const rt_vec4 &p0 = data->vertexPos_[v0], &p1 = data->vertexPos_[v1], &p2 = data->vertexPos_[v2];
     const int mesh = data->vertexMeshId_[v0]; // as mytracer_gpu.cu:492
     if (mesh < 0 || mesh >= num_meshes) {
-      err = "flatten: vertexMeshId_ out of range in triangle " + std::to_string(i);
-      return RT_ERR_BAD_SCENE;
+      fail_at(i, RT_ERR_BAD_SCENE, "flatten: vertexMeshId_ out of range in triangle " + std::to_string(i));
+      break;
     }
     TriExact &e = exact[i];
     e.p0[0] = p0.x; e.p0[1] = p0.y; e.p0[2] = p0.z;
@@ -203,7 +247,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     const double a = std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]);
     const double b = std::sqrt(e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2]);
     for (const rt_vec4 *p : {&p0, &p1, &p2}) {
-      extent = std::fmax(extent, std::fmax(std::fabs(p->x), std::fmax(std::fabs(p->y), std::fabs(p->z))));
+      extent_local = std::fmax(extent_local, std::fmax(std::fabs(p->x), std::fmax(std::fabs(p->y), std::fabs(p->z))));
     }
     TriFilter &f = filt[i];
     for (int k = 0; k < 3; ++k) {
@@ -232,20 +276,27 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     }
     if (data->meshTexWidth_[mesh] != -1) {
       if (!data->textureIdx_ || !data->textureCoordinatesU_ || !data->textureCoordinatesV_) {
-        err = "flatten: textured mesh but texture index/coordinate arrays are null";
-        return RT_ERR_INVALID_ARG;
+        fail_at(i, RT_ERR_INVALID_ARG, "flatten: textured mesh but texture index/coordinate arrays are null");
+        break;
       }
+      bool bad_uv = false;
       for (int k = 0; k < 3; ++k) {
         const int t = data->textureIdx_[3 * i + k];
-        if (t < 0 || t >= data->tTextCoordCount_) {
-          err = "flatten: texture index out of range in triangle " + std::to_string(i);
-          return RT_ERR_BAD_SCENE;
-        }
+        if (t < 0 || t >= data->tTextCoordCount_) { bad_uv = true; break; }
         s.uv[2 * k] = data->textureCoordinatesU_[t];
         s.uv[2 * k + 1] = data->textureCoordinatesV_[t];
       }
+      if (bad_uv) {
+        fail_at(i, RT_ERR_BAD_SCENE, "flatten: texture index out of range in triangle " + std::to_string(i));
+        break;
+      }
     }
   }
+  std::lock_guard<std::mutex> g(err_mu);
+  extent = std::fmax(extent, extent_local);
+  });
+  if (err_at >= 0) return err_code;
+  mark("triangle records");
   if (extent > 1e9) {
     // FP32 products could overflow: disable the filter (everything is confirmed in FP64)
     for (TriFilter &f : filt) f.k_det = std::numeric_limits<float>::infinity();
@@ -329,17 +380,21 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   const int num_nodes_q = (int)nodes.size();
   if (!(flags & RT_SCENE_REFERENCE_TOPOLOGY) && N > 2 && !root_is_leaf) {
     std::vector<float> plo(3 * (size_t)N), phi(3 * (size_t)N);
-    for (int i = 0; i < N; ++i) {
-      const TriExact &e = exact[i];
-      for (int k = 0; k < 3; ++k) {
-        plo[3 * (size_t)i + k] = round_down(std::fmin(e.p0[k], std::fmin(e.p1[k], e.p2[k])));
-        phi[3 * (size_t)i + k] = round_up(std::fmax(e.p0[k], std::fmax(e.p1[k], e.p2[k])));
+    parallel_ranges((size_t)N, 1 << 16, [&](size_t b, size_t e_) {
+      for (size_t i = b; i < e_; ++i) {
+        const TriExact &e = exact[i];
+        for (int k = 0; k < 3; ++k) {
+          plo[3 * i + k] = round_down(std::fmin(e.p0[k], std::fmin(e.p1[k], e.p2[k])));
+          phi[3 * i + k] = round_up(std::fmax(e.p0[k], std::fmax(e.p1[k], e.p2[k])));
+        }
       }
-    }
+    });
     std::vector<int> order;
     std::vector<SahNode> sn;
     int sah_depth = 0;
+    mark("primitive boxes");
     build_sah(plo.data(), phi.data(), N, order, sn, sah_depth);
+    mark("build_sah");
     if (!sn.empty() && sn[0].count == 0 && sah_depth <= kStackMax) {
       // interior nodes in DFS pre-order, as for the reference tree
       std::vector<NodeRec> trav;
@@ -372,7 +427,9 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
         trav[w.flat_idx] = n;
       }
       if (sah_depth > max_depth) max_depth = sah_depth;
+      mark("sah records + reorder");
       wide_tri = collapse_wide(sn, wide) == 0 ? (int)wide.size() : 0;
+      mark("collapse_wide");
       q_base = (int)trav.size();
       topology = 0;
       for (NodeRec &r : nodes) { // reference tree: interior child references move behind the traversal tree
@@ -384,11 +441,13 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
       // triangle records into traversal order
       std::vector<TriFilter> f2(N);
       std::vector<TriExact> e2(N);
-      for (int j = 0; j < N; ++j) {
-        const int i = order[j];
-        tri_id[j] = i; tri_pos[i] = j;
-        f2[j] = filt[i]; e2[j] = exact[i];
-      }
+      parallel_ranges((size_t)N, 1 << 16, [&](size_t b, size_t e_) {
+        for (size_t j = b; j < e_; ++j) {
+          const int i = order[j];
+          tri_id[j] = i; tri_pos[i] = (int)j;      // order is a permutation: every tri_pos slot is written once
+          f2[j] = filt[i]; e2[j] = exact[i];
+        }
+      });
       filt.swap(f2);
       exact.swap(e2);
     }
@@ -529,6 +588,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.num_texels = num_texels;
   h.scene_extent = (float)extent;
   h.box_extent = round_up(box_extent);
+  mark("objects");
   size_t off = align_up(sizeof(BlobHeader), kSectionAlign);
   h.off_nodes = off;   off = align_up(off + nodes.size() * sizeof(NodeRec), kSectionAlign);
   h.off_filter = off;  off = align_up(off + filt.size() * sizeof(TriFilter), kSectionAlign);
@@ -550,14 +610,15 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.q_base = q_base; h.num_nodes_q = num_nodes_q; h.topology = topology;
   h.root_max_x = N > 0 ? bvh->bb_max_[0].x : 0.0;
   h.total_bytes = off;
-  blob.assign(off, 0);
+  blob.clear();
+  blob.resize(off);   // value-initialised (zero): section padding is deterministic
   std::memcpy(blob.data(), &h, sizeof(h));
-  if (!nodes.empty()) std::memcpy(blob.data() + h.off_nodes, nodes.data(), nodes.size() * sizeof(NodeRec));
+  if (!nodes.empty()) parallel_copy(blob.data() + h.off_nodes, nodes.data(), nodes.size() * sizeof(NodeRec));
   if (!maxx.empty()) std::memcpy(blob.data() + h.off_maxx, maxx.data(), maxx.size() * sizeof(NodeMaxX));
   if (N > 0) {
-    std::memcpy(blob.data() + h.off_filter, filt.data(), filt.size() * sizeof(TriFilter));
-    std::memcpy(blob.data() + h.off_exact, exact.data(), exact.size() * sizeof(TriExact));
-    std::memcpy(blob.data() + h.off_shade, shade.data(), shade.size() * sizeof(TriShade));
+    parallel_copy(blob.data() + h.off_filter, filt.data(), filt.size() * sizeof(TriFilter));
+    parallel_copy(blob.data() + h.off_exact, exact.data(), exact.size() * sizeof(TriExact));
+    parallel_copy(blob.data() + h.off_shade, shade.data(), shade.size() * sizeof(TriShade));
     std::memcpy(blob.data() + h.off_tri_id, tri_id.data(), tri_id.size() * sizeof(int32_t));
     std::memcpy(blob.data() + h.off_tri_pos, tri_pos.data(), tri_pos.size() * sizeof(int32_t));
   }
@@ -566,12 +627,15 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   if (num_objects > 0) std::memcpy(blob.data() + h.off_objfilt, objf.data(), objf.size() * sizeof(ObjFilter));
   if (!obj_order.empty()) std::memcpy(blob.data() + h.off_obj_order, obj_order.data(), obj_order.size() * sizeof(int32_t));
   if (!lin_idx.empty()) std::memcpy(blob.data() + h.off_lin_idx, lin_idx.data(), lin_idx.size() * sizeof(int32_t));
-  if (!wide.empty()) std::memcpy(blob.data() + h.off_nodes4, wide.data(), wide.size() * sizeof(Node4Rec));
+  if (!wide.empty()) parallel_copy(blob.data() + h.off_nodes4, wide.data(), wide.size() * sizeof(Node4Rec));
   float *tx = reinterpret_cast<float *>(blob.data() + h.off_texels);
-  for (size_t t = 0; t < num_texels; ++t) {
-    const rt_vec4 &c = data->meshTexels_[t];
-    tx[4 * t] = (float)c.x; tx[4 * t + 1] = (float)c.y; tx[4 * t + 2] = (float)c.z; tx[4 * t + 3] = 1.0f;
-  }
+  parallel_ranges(num_texels, 1 << 18, [&](size_t b, size_t e_) {
+    for (size_t t = b; t < e_; ++t) {
+      const rt_vec4 &c = data->meshTexels_[t];
+      tx[4 * t] = (float)c.x; tx[4 * t + 1] = (float)c.y; tx[4 * t + 2] = (float)c.z; tx[4 * t + 3] = 1.0f;
+    }
+  });
+  mark("blob assembly");
   return RT_OK;
 }
 

@@ -50,7 +50,8 @@ def main():
             slot = pipe.submit(host_io=(f % 2 == 1))
             if rank == 0:
                 pipe.comm_done[f].synchronize()          # this frame's completion signal
-                got.append(pipe.frame(slot).cpu().numpy().copy())
+                if not (zc and f % 2 == 1):             # (zero copy: the pixels went to the host frame, not to rank 0's HBM)
+                    got.append(pipe.frame(slot).cpu().numpy().copy())
                 if f % 2 == 1:                          # the end-to-end frame: shared host block (zero copy) or rank 0's D2H
                     got.append(pipe.host_frame(slot).copy())
         pipe.drain()
