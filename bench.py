@@ -319,16 +319,31 @@ def run_b200(args):
     FLUSH = int(os.environ.get("RT_FLUSH_MB", "160")) * 1024 * 1024             # > 126 MB L2 (env: experiments only)
     # 0 = full-width grids (one GPU); half-width at 2-4 GPUs; quarter-width at 8
     ctas = int(os.environ.get("RT_CTAS_PER_SM", "0" if (world == 1 or big) else ("2" if world < 8 else "1")))
-    # the L2-evicting fill: on the frame's own stream at N = 1; at N > 1 a frame is so short (0.2 ms at 8 GPUs) that a
-    # 45 us fill serialised ahead of every kernel is 19 % of it, so it runs once per frame on a side stream, paced by the
-    # frames (A/B of the three modes in `flush_ab`)
-    flush_mode = os.environ.get("RT_FLUSH_MODE", "inline" if world == 1 else "side")
+    # Cold L2 at the start of every timed frame (timing rule: flush the L2 or use inputs larger than it).  Default
+    # "rotate": the frames cycle through identical COPIES of the flattened scene that add up to 1.4x the L2, so a copy is
+    # next touched only after the others have streamed through the cache - inputs larger than L2, no fill traffic inside
+    # the timed region.  A scene that is itself larger than the L2 needs neither ("big").  The evicting 160 MiB fill of
+    # round 1 stays selectable (RT_L2_MODE=inline: on the frame's stream ahead of its kernel; side: once per frame on a
+    # stream of its own) and is A/B-timed in `flush_ab` together with no eviction at all ("off").
+    l2_bytes = int(torch.cuda.get_device_properties(dev).L2_cache_size)
+    blob_bytes = int(info["blob_bytes"])
+    l2_mode = os.environ.get("RT_L2_MODE", "big" if blob_bytes > 1.4 * l2_bytes else "rotate")
+    ncopies = max(2, min(32, -(-int(1.4 * l2_bytes) // blob_bytes))) if blob_bytes <= 1.4 * l2_bytes else 1
+    copies = [scene]
+    if ncopies > 1:
+        p0, n0 = scene.blob_device()
+        copies += [rt.DeviceScene(lib=lib, blob_device_ptr=p0, blob_bytes=n0) for _ in range(ncopies - 1)]
     shared = rdist.SharedHostFrames(lib, W * H * 4 * (depth + 2), rank, world, dev) if world > 1 else None
 
     def make_pipe(mode):
-        return rdist.FramePipeline(lib, scene.handle, host, dev, W, H, depth=depth, ring=depth + 2, tile_chunk=chunk,
-                                   dyn_fraction=dyn_fraction, flush_bytes=FLUSH, ctas_per_sm=ctas, flush_mode=mode,
+        rot = mode == "rotate" and ncopies > 1
+        return rdist.FramePipeline(lib, [c.handle for c in copies] if rot else scene.handle, host, dev, W, H, depth=depth,
+                                   ring=depth + 2, tile_chunk=chunk, dyn_fraction=dyn_fraction,
+                                   flush_bytes=FLUSH if mode in ("inline", "side") else 0, ctas_per_sm=ctas,
+                                   flush_mode=mode if mode in ("inline", "side") else "off",
                                    spp_grid=spp_grid, shared_host=shared, flags=pflags)
+    flush_mode = l2_mode
+    flush_buf = torch.empty(FLUSH, dtype=torch.uint8, device=dev) if FLUSH else None   # serial single-frame timings
     pipe = make_pipe(flush_mode)
     nl = pipe.nl
     stream = torch.cuda.current_stream()
@@ -390,7 +405,7 @@ def run_b200(args):
     e2e_frame_sha = None
     if world == 1:
         # the C ABI's pipelined host-buffer call: rt_frame_submit(host lights, pinned host frame) / rt_frame_wait
-        qopts = capi.FrameQueueOpts(depth, ctas, 0, 0, FLUSH if flush_mode != "off" else 0)
+        qopts = capi.FrameQueueOpts(depth, ctas, 0, 0, FLUSH if flush_mode in ("inline", "side") else 0)
         q = C.c_void_p()
         capi.check(lib.rt_frame_queue_create(scene.handle, W, H, C.byref(qopts), C.byref(q)), lib)
         hbuf = C.c_void_p()
@@ -402,6 +417,8 @@ def run_b200(args):
 
         def q_submit():
             k = q_submit.n % nring
+            if flush_mode == "rotate" and ncopies > 1:       # the next frame renders the next copy of the scene
+                capi.check(lib.rt_frame_queue_bind(q, copies[q_submit.n % ncopies].handle), lib)
             capi.check(lib.rt_frame_submit(q, C.byref(cam), lp.ctypes.data_as(capi.Vec4_p), lc.ctypes.data_as(capi.Vec4_p), nl,
                                            C.byref(qparams), C.c_void_p(hbuf.value + k * W * H * 4), C.byref(tick)), lib)
             q_submit.n += 1
@@ -442,10 +459,10 @@ def run_b200(args):
 
     # ---- A/B of the L2 flush modes (N > 1): what the per-frame 160 MiB fill costs -------------------------------
     flush_ab = None
-    if world > 1 and not args.no_ab:
+    if not args.no_ab and not big:
         flush_ab = {}
         n_ab = max(10, args.steps // 2)
-        for mode in ("inline", "side", "off"):
+        for mode in ("rotate", "inline", "side", "off"):
             if mode == flush_mode:
                 flush_ab[mode] = ms_per_step
                 continue
@@ -481,8 +498,8 @@ def run_b200(args):
     capi.check(lib.rt_scene_set_launch_width(scene.handle, 0), lib)     # one frame alone gets the whole machine
     kern_ms = []
     def evict():
-        if pipe.flush is not None:
-            pipe.flush.fill_(1)
+        if flush_buf is not None:
+            flush_buf.fill_(1)
     for i in range(5 if big else 8):
         evict()
         capi.check(lib.rt_render_device(scene.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
@@ -540,6 +557,30 @@ def run_b200(args):
         binary_nodes = {"kernel_ms_single_frame": k3, "mrays": rays_frame / (k3 * 1e-3) / 1e6,
                         "note": "RT_FLAG_BINARY_NODES, same frame bit for bit; compare with latency_ms_single_frame"}
 
+    # ---- A/B: ordinary rays on the 8-wide twin of the triangle tree (N = 1, serial frames) ------------------------------
+    nodes8 = None
+    if world == 1 and not args.no_ab and info.get("num_nodes_wide8", 0) > 0:
+        p8 = host.params(spp_grid=spp_grid, tile=pipe.tile, flags=capi.RT_FLAG_NO_CLEAR | capi.RT_FLAG_NODES8 | capi.RT_FLAG_MEGAKERNEL)
+        ms8 = []
+        for i in range(4 if big else 8):
+            evict()
+            capi.check(lib.rt_render_device(scene.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
+                                            C.byref(p8), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
+            ms8.append(scene.last_kernel_ms())
+        k8 = sum(ms8[2:]) / len(ms8[2:])
+        c8p = host.params(spp_grid=spp_grid, tile=pipe.tile, flags=capi.RT_FLAG_COUNTERS | capi.RT_FLAG_NODES8 | capi.RT_FLAG_MEGAKERNEL)
+        capi.check(lib.rt_render_device(scene.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
+                                        C.byref(c8p), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
+        c8 = capi.Counters()
+        capi.check(lib.rt_get_counters(scene.handle, C.byref(c8)), lib)
+        c8 = c8.as_dict()
+        f8 = 24 * c8["box_tests"] + 48 * c8["tri_filter"] + (60 * nl + 20) * c8["shaded_hits"]
+        nodes8 = {"kernel_ms_single_frame": k8, "mrays": rays_frame / (k8 * 1e-3) / 1e6, "box_tests": c8["box_tests"],
+                  "nodes_visited": c8["nodes_visited"], "flops_per_launch": f8,
+                  "fp32_frac_single_frame": f8 / (k8 * 1e-3) / 1e12 / (148 * 128 * 2 * float(measured_peaks().get("sm_max_mhz", 1965.0)) * 1e6 / 1e12),
+                  "note": "RT_FLAG_NODES8 (256-byte eight-child records), same frame bit for bit; compare with "
+                          "latency_ms_single_frame / roofline.frac_single_frame"}
+
     wide = tot.get("nodes4_visited", 0) > 0      # ordinary rays walked the 4-wide tree (render_kernel<K_WIDE>)
     # ---- roofline of the render kernel -------------------------------------------------------------
     peaks = measured_peaks()
@@ -591,10 +632,14 @@ def run_b200(args):
                        "traversal_records": info["num_nodes_traversal"],
                        "node_width": 4 if wide else 2, "wide_records": info.get("num_nodes_wide", 0),
                        "lights": nl, "max_depth": desc.max_depth, "spp": spp_grid * spp_grid,
-                       "l2": {"inline": "flushed before every timed frame (160 MiB fill on the frame's stream)",
-                              "side": "flushed once per timed frame: 160 MiB fill on a side stream, paced by the frames "
-                                      "(A/B against the in-line fill and no fill in flush_ab)",
-                              "off": "NOT flushed (experiment)"}[pipe.flush_mode],
+                       "l2": {"rotate": "inputs larger than L2: %d identical copies of the flattened scene (%.0f MB, L2 %.0f MB), "
+                                        "frame f renders copy f %% %d, so every frame starts with its scene out of cache; no "
+                                        "fill inside the timed region (flush_ab: the 160 MiB fill in-line / on a side stream, and "
+                                        "no eviction)" % (ncopies, ncopies * blob_bytes / 1e6, l2_bytes / 1e6, ncopies),
+                              "big": "inputs larger than L2: the flattened scene is %.0f MB (L2 %.0f MB); no flush" % (blob_bytes / 1e6, l2_bytes / 1e6),
+                              "inline": "flushed before every timed frame (160 MiB fill on the frame's stream)",
+                              "side": "flushed once per timed frame: 160 MiB fill on a side stream, paced by the frames",
+                              "off": "NOT evicted (experiment)"}[flush_mode],
                        "timing": "steady-state window: value is THROUGHPUT with frames_in_flight frames in flight "
                                  "(one frame alone: latency_ms_single_frame)",
                        "frames_in_flight": pipe.depth, "ctas_per_sm_per_frame": pipe.ctas_per_sm or "all",
@@ -606,6 +651,7 @@ def run_b200(args):
             "latency_ms_single_frame": max(rank_ms),
             "other_tree": other_tree,
             "binary_nodes": binary_nodes,
+            "nodes8": nodes8,
             "flush_ab": flush_ab,
             "rays_per_frame": {k: tot[k] for k in ("rays_primary", "rays_shadow", "rays_reflect")},
             "counters": tot,

@@ -139,6 +139,9 @@ typedef struct rt_render_params {
                                   the one persistent kernel; frames the wavefront does not cover (pixel lists, dynamic
                                   tile queue, RT_FLAG_COUNTERS, > 30 lights) fall back to the persistent kernel.
                                   RT_B200_PIPELINE=wavefront in the environment selects it for every frame. */
+#define RT_FLAG_NODES8      64 /* A/B: ordinary rays walk the 8-wide twin of the triangle tree (256-byte records, eight slab
+                                  tests per step) instead of the 4-wide one; scenes without one (a tree over analytic
+                                  spheres, tiny meshes) ignore the flag.  RT_B200_NODES=8 selects it for every frame. */
 #define RT_FLAG_MEGAKERNEL  32 /* always the one persistent kernel (overrides RT_B200_PIPELINE) */
 
 /* Output buffers; any pointer may be NULL.  All are W*H entries, index y*W + x
@@ -163,6 +166,7 @@ typedef struct rt_counters {
                                         the light's contribution is exactly zero whatever the occlusion */
   unsigned long long shadow_occluded;   /* shadow rays that found an occluder */
   unsigned long long nodes4_visited;    /* of nodes_visited: 128-byte four-child records (4-wide tree) */
+  unsigned long long nodes8_visited;    /* of nodes_visited: 256-byte eight-child records (8-wide tree) */
 } rt_counters;
 
 typedef struct rt_scene_info {
@@ -176,6 +180,7 @@ typedef struct rt_scene_info {
   int topology;            /* 0: SAH traversal tree + reference tree for d.x == 0 rays; 1: reference tree only */
   int num_nodes_traversal; /* records of the tree ordinary rays walk */
   int num_nodes_wide;      /* 128-byte four-child records of the 4-wide twins of the traversal trees (0: none) */
+  int num_nodes_wide8;     /* 256-byte eight-child records of the triangle tree's 8-wide twin (0: none) */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene;
@@ -260,6 +265,9 @@ int rt_frame_submit(rt_frame_queue *queue, const rt_camera *camera, const rt_vec
                     const rt_vec4 *lights_color, int num_lights, const rt_render_params *params,
                     uint8_t *rgba8_host, long long *ticket);
 int rt_frame_wait(rt_frame_queue *queue, long long ticket, double *done_ms);
+/* The frames submitted from now on render `scene` (a host that switches scenes between frames; frames in flight are
+ * not affected). */
+int rt_frame_queue_bind(rt_frame_queue *queue, rt_scene *scene);
 int rt_frame_queue_destroy(rt_frame_queue *queue);
 /* Pinned, device-mapped host memory for frames: allocated here, or an existing block (e.g. a POSIX shared-memory
  * segment that every rank's process maps) registered with the CUDA driver.  dptr (may be NULL): its device

@@ -5,7 +5,7 @@ from __future__ import annotations
 import ctypes as C
 
 BLOB_MAGIC = 0x42325452
-BLOB_VERSION = 11
+BLOB_VERSION = 12
 
 
 class BlobHeader(C.Structure):
@@ -24,6 +24,7 @@ class BlobHeader(C.Structure):
         ("obj_root", C.c_int32), ("num_nodes_obj", C.c_int32), ("num_obj_tree", C.c_int32), ("num_lin", C.c_int32),
         ("off_nodes4", C.c_uint64),
         ("num_nodes4_tri", C.c_int32), ("obj_root4", C.c_int32), ("pad_h", C.c_int32 * 2),
+        ("off_nodes8", C.c_uint64), ("num_nodes8", C.c_int32), ("pad_8", C.c_int32),
     ]
 
 

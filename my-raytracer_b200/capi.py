@@ -16,7 +16,7 @@ RT_OK = 0
 RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_BAD_SCENE, RT_ERR_LIMIT, RT_ERR_OOM = 1, 2, 3, 4, 5, 6
 RT_SPHERE, RT_PLANE = 0, 1
 RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR, RT_FLAG_BINARY_NODES = 1, 2, 4, 8
-RT_FLAG_WAVEFRONT, RT_FLAG_MEGAKERNEL = 16, 32
+RT_FLAG_WAVEFRONT, RT_FLAG_MEGAKERNEL, RT_FLAG_NODES8 = 16, 32, 64
 RT_SCENE_REFERENCE_TOPOLOGY = 1
 
 c_int_p = C.POINTER(C.c_int)
@@ -96,7 +96,7 @@ class Counters(C.Structure):
     _fields_ = [(n, C.c_ulonglong) for n in (
         "rays_primary", "rays_shadow", "rays_reflect", "box_tests", "tri_filter", "tri_exact",
         "object_tests", "shaded_hits", "texel_fetches", "nodes_visited", "shadow_trivial",
-        "shadow_occluded", "nodes4_visited")]
+        "shadow_occluded", "nodes4_visited", "nodes8_visited")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -107,7 +107,7 @@ class SceneInfo(C.Structure):
                 ("num_nodes_ref", C.c_int), ("num_nodes_flat", C.c_int), ("max_depth_bvh", C.c_int),
                 ("max_leaf_size", C.c_int), ("blob_bytes", C.c_size_t), ("flatten_ms", C.c_double),
                 ("upload_ms", C.c_double), ("topology", C.c_int), ("num_nodes_traversal", C.c_int),
-                ("num_nodes_wide", C.c_int)]
+                ("num_nodes_wide", C.c_int), ("num_nodes_wide8", C.c_int)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -150,6 +150,7 @@ PROTOTYPES = {
     "rt_frame_submit": (C.c_int, [C.c_void_p, C.POINTER(Camera), Vec4_p, Vec4_p, C.c_int, C.POINTER(RenderParams),
                                   C.c_void_p, C.POINTER(C.c_longlong)]),
     "rt_frame_wait": (C.c_int, [C.c_void_p, C.c_longlong, c_double_p]),
+    "rt_frame_queue_bind": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rt_frame_queue_destroy": (C.c_int, [C.c_void_p]),
     "rt_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "rt_host_free": (C.c_int, [C.c_void_p]),

@@ -75,6 +75,8 @@ struct rt_scene {
   int grid_plain = 0, grid_count = 0;
   int grid_wide = 0, grid_wide_count = 0; // K_WIDE kernels (scenes whose trees all have 4-wide twins)
   bool wide_ok = false;
+  bool wide8_ok = false, wide8_default = false;   // 8-wide twin usable; RT_B200_NODES=8
+  int grid_wide8 = 0, grid_wide8_count = 0;
   int sm_count = 0, ctas_per_sm = 0; // ctas_per_sm: 0 = every resident slot (rt_scene_set_launch_width)
   size_t extra_smem = 0;
   rt_counters counters;
@@ -139,6 +141,15 @@ __global__ void validate_blob_kernel(SceneView v, int num_obj_tree, int *bad) {
       else ok = ok && (long long)r.ref[k] + r.cnt[k] <= limit;
     }
   }
+  if (i < v.num_nodes8) {
+    const Node8Rec r = v.nodes8[i];
+    for (int k = 0; k < 8; ++k) {
+      if (r.ref[k] == -1 && r.cnt[k] == 0) continue; // empty slot
+      if (r.cnt[k] < 0 || r.ref[k] < 0) ok = false;
+      else if (r.cnt[k] == 0) ok = ok && r.ref[k] < v.num_nodes8;
+      else ok = ok && (long long)r.ref[k] + r.cnt[k] <= v.num_tris;
+    }
+  }
   if (i < v.num_tris) {
     ok = ok && (unsigned)v.tri_id[i] < (unsigned)v.num_tris && (unsigned)v.tri_pos[i] < (unsigned)v.num_tris;
     ok = ok && (unsigned)v.shade[i].mesh < (unsigned)v.num_meshes;
@@ -166,6 +177,8 @@ int adopt_blob(rt_scene *s) {
   s->view.num_nodes4 = h.num_nodes4;
   s->view.obj_root4 = h.obj_root4; s->view.num_nodes4_tri = h.num_nodes4_tri;
   s->view.nodes4 = h.num_nodes4 > 0 ? reinterpret_cast<const Node4Rec *>(b + h.off_nodes4) : nullptr;
+  s->view.nodes8 = h.num_nodes8 > 0 ? reinterpret_cast<const Node8Rec *>(b + h.off_nodes8) : nullptr;
+  s->view.num_nodes8 = h.num_nodes8;
   s->view.texels = reinterpret_cast<const float *>(b + h.off_texels);
   s->view.num_nodes = h.num_nodes; s->view.num_tris = h.num_tris;
   s->view.num_meshes = h.num_meshes; s->view.num_objects = h.num_objects;
@@ -181,6 +194,7 @@ int adopt_blob(rt_scene *s) {
     RT_CUDA(cudaMemset(d_bad, 0, sizeof(int)));
     long long n = h.num_nodes;
     if (h.num_nodes4 > n) n = h.num_nodes4;
+    if (h.num_nodes8 > n) n = h.num_nodes8;
     if (h.num_tris > n) n = h.num_tris;
     if (h.num_objects > n) n = h.num_objects;
     if (n > 0) validate_blob_kernel<<<(unsigned)((n + 255) / 256), 256>>>(s->view, h.num_obj_tree, d_bad);
@@ -271,6 +285,20 @@ int adopt_blob(rt_scene *s) {
     }
     if (const char *e = std::getenv("RT_B200_PIPELINE")) s->wavefront_default = std::strcmp(e, "wavefront") == 0;
   }
+  s->wide8_ok = s->wide_ok && wide8_usable(s->view);
+  if (s->wide8_ok) {
+    int o8 = 0, o8c = 0;
+    const void *k8 = (const void *)render_kernel<K_WIDE | K_WIDE8>, *k8c = (const void *)render_kernel<K_WIDE | K_WIDE8 | K_COUNT>;
+    if (s->extra_smem) {
+      RT_CUDA(cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+      RT_CUDA(cudaFuncSetAttribute(k8c, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->extra_smem));
+    }
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o8, k8, kBlockThreads, s->extra_smem));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o8c, k8c, kBlockThreads, s->extra_smem));
+    s->grid_wide8 = prop.multiProcessorCount * (o8 > 0 ? o8 : 1);
+    s->grid_wide8_count = prop.multiProcessorCount * (o8c > 0 ? o8c : 1);
+    if (const char *e = std::getenv("RT_B200_NODES")) s->wide8_default = std::atoi(e) == 8;
+  }
   s->sm_count = prop.multiProcessorCount;
   s->grid_plain = prop.multiProcessorCount * (occ0 > 0 ? occ0 : 1);
   s->grid_count = prop.multiProcessorCount * (occ1 > 0 ? occ1 : 1);
@@ -278,6 +306,8 @@ int adopt_blob(rt_scene *s) {
     int gmax = s->grid_plain > s->grid_count ? s->grid_plain : s->grid_count;
     if (s->grid_wide > gmax) gmax = s->grid_wide;
     if (s->grid_wide_count > gmax) gmax = s->grid_wide_count;
+    if (s->grid_wide8 > gmax) gmax = s->grid_wide8;
+    if (s->grid_wide8_count > gmax) gmax = s->grid_wide8_count;
     const size_t threads = (size_t)gmax * kBlockThreads;
     RT_CUDA(cudaMalloc(&s->d_scratch_d, threads * CD_NUM * sizeof(double)));
     RT_CUDA(cudaMalloc(&s->d_scratch_i, threads * CI_NUM * sizeof(int)));
@@ -289,6 +319,7 @@ int adopt_blob(rt_scene *s) {
   s->info.topology = h.topology;
   s->info.num_nodes_traversal = h.topology == 0 ? h.q_base : h.num_nodes;
   s->info.num_nodes_wide = h.num_nodes4;
+  s->info.num_nodes_wide8 = h.num_nodes8;
   std::memset(&s->counters, 0, sizeof(s->counters));
   return RT_OK;
 }
@@ -336,14 +367,18 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
   // frames in flight share the machine: with ctas_per_sm = k each launch takes k of the resident CTA slots of
   // every SM, so several persistent grids run side by side instead of queueing for each other's slots
   const bool wide = s->wide_ok && !(fp.flags & RT_FLAG_BINARY_NODES);
+  const bool wide8 = wide && s->wide8_ok && ((fp.flags & RT_FLAG_NODES8) || s->wide8_default);
   int gc = wide ? s->grid_wide_count : s->grid_count, gp = wide ? s->grid_wide : s->grid_plain;
+  if (wide8) { gc = s->grid_wide8_count; gp = s->grid_wide8; }
   if (s->ctas_per_sm > 0) {
     const int lim = s->sm_count * s->ctas_per_sm;
     gc = gc < lim ? gc : lim;
     gp = gp < lim ? gp : lim;
   }
   const bool obj = s->hdr.obj_root >= 0; // tree over analytic spheres: the kernel variant that can walk it
-  switch ((count ? K_COUNT : 0) | (obj ? K_OBJ : 0) | (wide ? K_WIDE : 0)) {
+  switch ((count ? K_COUNT : 0) | (obj ? K_OBJ : 0) | (wide ? K_WIDE : 0) | (wide8 ? K_WIDE8 : 0)) {
+    case K_WIDE | K_WIDE8: render_kernel<K_WIDE | K_WIDE8><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+    case K_WIDE | K_WIDE8 | K_COUNT: render_kernel<K_WIDE | K_WIDE8 | K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
     case 0: render_kernel<0><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
     case K_COUNT: render_kernel<K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;
     case K_OBJ: render_kernel<K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
@@ -445,6 +480,7 @@ int fetch_counters(rt_scene *s, cudaStream_t st) {
   c.shadow_trivial = h[C_SHADOW_TRIVIAL];
   c.shadow_occluded = h[C_SHADOW_OCCLUDED];
   c.nodes4_visited = h[C_NODES4];
+  c.nodes8_visited = h[C_NODES8];
   return RT_OK;
 }
 
@@ -890,6 +926,12 @@ int rt_frame_submit(rt_frame_queue *q, const rt_camera *camera, const rt_vec4 *l
   sl.ticket = t;
   q->submitted = t + 1;
   if (ticket) *ticket = t;
+  return RT_OK;
+}
+
+int rt_frame_queue_bind(rt_frame_queue *q, rt_scene *scene) {
+  if (!q || !scene) { set_error("rt_frame_queue_bind: null argument"); return RT_ERR_INVALID_ARG; }
+  q->scene = scene;   // frames already submitted keep the scene they were launched on
   return RT_OK;
 }
 

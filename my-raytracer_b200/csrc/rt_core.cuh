@@ -86,7 +86,8 @@ enum Special : int { S_XPAR = 1, S_OBJ = 2 };
 // that code (its mere presence in the leaf path costs 3 % on the Office scene).
 // K_WIDE = ordinary rays walk the 4-wide twins of the traversal trees (Node4Rec, trav_step4): the triangle tree's
 // and, with K_OBJ, the object tree's (the host picks K_WIDE only when every tree the scene has owns a twin).
-enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2, K_WIDE = 4 };
+// K_WIDE8 = ordinary rays walk the 8-wide twin of the triangle tree (Node8Rec, trav_step8); never together with K_OBJ.
+enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2, K_WIDE = 4, K_WIDE8 = 8 };
 
 struct Mat {
   D3 ka, ks;
@@ -408,6 +409,21 @@ template <int COUNT, bool XP, int S> RT_HD void trav_step(const Ctx &c, Hot &H, 
   H.sp = sp;
 }
 
+// Experiment (RT_PREFETCH_PUSH, out-of-cache scenes): when a child is postponed, ask L2 for its record so that the pop
+// finds it on chip.  0 = off (default: a loss while the tree is L1/L2 resident, profiles/r01_variants.md).
+#ifndef RT_PREFETCH_PUSH
+#define RT_PREFETCH_PUSH 0
+#endif
+RT_HD void prefetch_rec(const void *base, int ref, unsigned bytes) {
+#if defined(__CUDA_ARCH__) && RT_PREFETCH_PUSH
+  const char *p = reinterpret_cast<const char *>(base) + (size_t)(unsigned)ref * bytes;
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  if (bytes > 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+#else
+  (void)base; (void)ref; (void)bytes;
+#endif
+}
+
 // One step through the 4-wide tree (K_WIDE kernels, ordinary rays only): one 128-byte Node4Rec (four 32-byte
 // loads), four independent conservative slab tests (48 FMAs as 24 FFMA2, box_pair), hit leaf children intersected at
 // once, the nearest hit interior child next, the others pushed with their entry distances (culled when popped).  Half the
@@ -471,10 +487,10 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
     // nearest interior child next (first of equals); the others are pushed in child order (no branches)
     const bool k0 = u0 == m, k1 = !k0 && u1 == m, k2 = !k0 && !k1 && u2 == m;
     node = k0 ? r0 : (k1 ? r1 : (k2 ? r2 : r3));
-    if (h0 && !k0) { stk[sp].ref = r0; stk[sp].tn = t0; ++sp; }
-    if (h1 && !k1) { stk[sp].ref = r1; stk[sp].tn = t1; ++sp; }
-    if (h2 && !k2) { stk[sp].ref = r2; stk[sp].tn = t2; ++sp; }
-    if (h3 && (k0 || k1 || k2)) { stk[sp].ref = r3; stk[sp].tn = t3; ++sp; }
+    if (h0 && !k0) { stk[sp].ref = r0; stk[sp].tn = t0; ++sp; prefetch_rec(c.sv.nodes4, r0, 128u); }
+    if (h1 && !k1) { stk[sp].ref = r1; stk[sp].tn = t1; ++sp; prefetch_rec(c.sv.nodes4, r1, 128u); }
+    if (h2 && !k2) { stk[sp].ref = r2; stk[sp].tn = t2; ++sp; prefetch_rec(c.sv.nodes4, r2, 128u); }
+    if (h3 && (k0 || k1 || k2)) { stk[sp].ref = r3; stk[sp].tn = t3; ++sp; prefetch_rec(c.sv.nodes4, r3, 128u); }
   } else {
     node = -1;
     while (sp > 0) {
@@ -487,10 +503,99 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   H.sp = sp;
 }
 
+// One step through the 8-wide tree (K_WIDE8 kernels, ordinary rays, triangle tree only): one 256-byte Node8Rec (eight
+// 32-byte loads), eight independent conservative slab tests (48 FFMA2), hit leaf children intersected at once, the
+// nearest hit interior child next, the others pushed in child order with their entry distances.  A ray of the Office scene
+// needs 6 of these instead of 10 four-wide steps: fewer dependent load -> test -> vote chains, more independent
+// arithmetic inside each.
+RT_HD int sel8(int k, int a0, int a1, int a2, int a3, int a4, int a5, int a6, int a7) {
+  const int lo = (k & 2) ? ((k & 1) ? a3 : a2) : ((k & 1) ? a1 : a0);
+  const int hi = (k & 2) ? ((k & 1) ? a7 : a6) : ((k & 1) ? a5 : a4);
+  return (k & 4) ? hi : lo;
+}
+template <int COUNT, int S>
+RT_HD void trav_step8(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
+  const char *np = reinterpret_cast<const char *>(c.sv.nodes8) + (size_t)(unsigned)H.node * 256u;
+  const W8 q0 = ld_w8(np), q1 = ld_w8(np + 32), q2 = ld_w8(np + 64), q3 = ld_w8(np + 96), q4 = ld_w8(np + 128),
+           q5 = ld_w8(np + 160), q6 = ld_w8(np + 192), q7 = ld_w8(np + 224);
+  bump<COUNT>(c, C_NODES);
+  bump<COUNT>(c, C_NODES8);
+  // q0..q5 = the four child pairs, 12 words each | q6 = ref[8] | q7 = cnt[8]
+  float w[48];
+  RT_UNROLL
+  for (int k = 0; k < 8; ++k) {
+    w[k] = w2f(q0.w[k]); w[8 + k] = w2f(q1.w[k]); w[16 + k] = w2f(q2.w[k]);
+    w[24 + k] = w2f(q3.w[k]); w[32 + k] = w2f(q4.w[k]); w[40 + k] = w2f(q5.w[k]);
+  }
+  const int r0 = (int)q6.w[0], r1 = (int)q6.w[1], r2 = (int)q6.w[2], r3 = (int)q6.w[3], r4 = (int)q6.w[4],
+            r5 = (int)q6.w[5], r6 = (int)q6.w[6], r7 = (int)q6.w[7];
+  const int n0 = (int)q7.w[0], n1 = (int)q7.w[1], n2 = (int)q7.w[2], n3 = (int)q7.w[3], n4 = (int)q7.w[4],
+            n5 = (int)q7.w[5], n6 = (int)q7.w[6], n7 = (int)q7.w[7];
+  if (COUNT & K_COUNT)
+    bump<COUNT>(c, C_BOX, 2u + (unsigned)(r2 >= 0) + (unsigned)(r3 >= 0) + (unsigned)(r4 >= 0) + (unsigned)(r5 >= 0) +
+                              (unsigned)(r6 >= 0) + (unsigned)(r7 >= 0));
+  float t0, t1, t2, t3, t4, t5, t6, t7;
+  bool h0, h1, h2, h3, h4, h5, h6, h7;
+  box_pair(H.rf, w, H.thiS, t0, t1, h0, h1);
+  box_pair(H.rf, w + 12, H.thiS, t2, t3, h2, h3);
+  box_pair(H.rf, w + 24, H.thiS, t4, t5, h4, h5);
+  box_pair(H.rf, w + 36, H.thiS, t6, t7, h6, h7);
+  const unsigned hm = (h0 ? 1u : 0u) | (h1 ? 2u : 0u) | (h2 ? 4u : 0u) | (h3 ? 8u : 0u) | (h4 ? 16u : 0u) | (h5 ? 32u : 0u) |
+                      (h6 ? 64u : 0u) | (h7 ? 128u : 0u);
+  const unsigned leafm = (n0 > 0 ? 1u : 0u) | (n1 > 0 ? 2u : 0u) | (n2 > 0 ? 4u : 0u) | (n3 > 0 ? 8u : 0u) |
+                         (n4 > 0 ? 16u : 0u) | (n5 > 0 ? 32u : 0u) | (n6 > 0 ? 64u : 0u) | (n7 > 0 ? 128u : 0u);
+  unsigned lm = hm & leafm;
+  const unsigned im = hm & ~leafm;
+  while (lm) {
+    // runs of neighbouring hit leaves own adjacent triangle ranges: one loop per run
+    const int k = first_bit(lm);
+    const unsigned run = lm >> k;
+    const int len = first_bit(~run);                       // >= 1
+    const int e = k + len - 1;
+    lm &= ~(((1u << len) - 1u) << k);
+    const int first = sel8(k, r0, r1, r2, r3, r4, r5, r6, r7);
+    const int last = sel8(e, r0, r1, r2, r3, r4, r5, r6, r7) + sel8(e, n0, n1, n2, n3, n4, n5, n6, n7);
+    leaf_test<COUNT, false>(c, H, C, first, last);
+    if (H.found) { H.node = -1; return; }
+  }
+  int node, sp = H.sp;
+  if (im) {
+    const float INF = 3.0e38f;
+    const float u0 = (im & 1u) ? t0 : INF, u1 = (im & 2u) ? t1 : INF, u2 = (im & 4u) ? t2 : INF, u3 = (im & 8u) ? t3 : INF;
+    const float u4 = (im & 16u) ? t4 : INF, u5 = (im & 32u) ? t5 : INF, u6 = (im & 64u) ? t6 : INF, u7 = (im & 128u) ? t7 : INF;
+    const float m = fminf(fminf(fminf(u0, u1), fminf(u2, u3)), fminf(fminf(u4, u5), fminf(u6, u7)));
+    // nearest interior child next (first of equals); the others are pushed in child order
+    const unsigned eq = (u0 == m ? 1u : 0u) | (u1 == m ? 2u : 0u) | (u2 == m ? 4u : 0u) | (u3 == m ? 8u : 0u) |
+                        (u4 == m ? 16u : 0u) | (u5 == m ? 32u : 0u) | (u6 == m ? 64u : 0u) | (u7 == m ? 128u : 0u);
+    const unsigned pickm = (eq & im) & (0u - (eq & im));   // lowest set bit
+    const unsigned rest = im & ~pickm;
+    node = sel8(first_bit(pickm), r0, r1, r2, r3, r4, r5, r6, r7);
+    if (rest & 1u) { stk[sp].ref = r0; stk[sp].tn = t0; ++sp; prefetch_rec(c.sv.nodes8, r0, 256u); }
+    if (rest & 2u) { stk[sp].ref = r1; stk[sp].tn = t1; ++sp; prefetch_rec(c.sv.nodes8, r1, 256u); }
+    if (rest & 4u) { stk[sp].ref = r2; stk[sp].tn = t2; ++sp; prefetch_rec(c.sv.nodes8, r2, 256u); }
+    if (rest & 8u) { stk[sp].ref = r3; stk[sp].tn = t3; ++sp; prefetch_rec(c.sv.nodes8, r3, 256u); }
+    if (rest & 16u) { stk[sp].ref = r4; stk[sp].tn = t4; ++sp; prefetch_rec(c.sv.nodes8, r4, 256u); }
+    if (rest & 32u) { stk[sp].ref = r5; stk[sp].tn = t5; ++sp; prefetch_rec(c.sv.nodes8, r5, 256u); }
+    if (rest & 64u) { stk[sp].ref = r6; stk[sp].tn = t6; ++sp; prefetch_rec(c.sv.nodes8, r6, 256u); }
+    if (rest & 128u) { stk[sp].ref = r7; stk[sp].tn = t7; ++sp; prefetch_rec(c.sv.nodes8, r7, 256u); }
+  } else {
+    node = -1;
+    while (sp > 0) {
+      --sp;
+      const StackEntry e2 = stk[sp];
+      if (e2.tn <= H.thiS) { node = e2.ref; break; }
+    }
+  }
+  H.node = node;
+  H.sp = sp;
+}
+
 // host/test build: run this lane's ray to completion
 template <int COUNT, int S> RT_HD void traverse(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   do {
-    if (COUNT & K_WIDE) {
+    if (COUNT & K_WIDE8) {
+      while (H.node >= 0) trav_step8<COUNT>(c, H, C, stk);
+    } else if (COUNT & K_WIDE) {
       while (H.node >= 0) trav_step4<COUNT>(c, H, C, stk); // ordinary rays; d.x == 0 rays are parked (node <= -2)
     }
     unpark(H.node);

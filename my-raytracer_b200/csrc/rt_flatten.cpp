@@ -17,6 +17,7 @@
 #include <cstring>
 #include <initializer_list>
 #include <limits>
+#include <type_traits>
 
 namespace rtb {
 namespace {
@@ -307,7 +308,9 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   // tree's left-to-right order and leaf ranges ascend) until there are four or none is interior.  Records are appended
   // to `out` in DFS pre-order; returns the root's record index.  The kernel pushes at most (interior children - 1)
   // entries per visit; if the worst root-to-leaf sum does not fit the traversal stack the twin is dropped (-1).
-  auto collapse_wide = [&](const std::vector<SahNode> &sn, std::vector<Node4Rec> &out) -> int {
+  auto collapse_wide = [&](const std::vector<SahNode> &sn, auto &out) -> int {
+    using Rec = typename std::decay_t<decltype(out)>::value_type;   // Node4Rec or Node8Rec: same fields, W children
+    constexpr int W = (int)(sizeof(Rec::ref) / sizeof(int32_t));
     struct W4 { int sah_node, rec, stack_before; };
     std::vector<W4> todo4;
     const size_t base4 = out.size();
@@ -322,9 +325,9 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     while (!todo4.empty()) {
       const W4 w = todo4.back();
       todo4.pop_back();
-      int slot[4], ns = 2;
+      int slot[W], ns = 2;
       slot[0] = sn[w.sah_node].left; slot[1] = sn[w.sah_node].right;
-      while (ns < 4) {
+      while (ns < W) {
         int pick = -1;
         double best_area = -1.0;
         for (int k = 0; k < ns; ++k)
@@ -335,9 +338,10 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
         slot[pick] = l; slot[pick + 1] = r;
         ++ns;
       }
-      Node4Rec n;
-      int child_rec[4] = {-1, -1, -1, -1}, interior = 0;
-      for (int k = 0; k < 4; ++k) {
+      Rec n;
+      int child_rec[W], interior = 0;
+      for (int k = 0; k < W; ++k) child_rec[k] = -1;
+      for (int k = 0; k < W; ++k) {
         float ctr[3] = {0.0f, 0.0f, 0.0f}, half[3] = {-1e30f, -1e30f, -1e30f};
         if (k < ns) {
           const SahNode &cb = sn[slot[k]];
@@ -360,7 +364,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
       }
       const int stack_after = w.stack_before + (interior > 1 ? interior - 1 : 0);
       if (stack_after > worst_stack) worst_stack = stack_after;
-      for (int k = 3; k >= 0; --k)
+      for (int k = W - 1; k >= 0; --k)
         if (child_rec[k] >= 0) todo4.push_back({slot[k], child_rec[k], stack_after});
       out[w.rec] = n;
     }
@@ -376,6 +380,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   for (int i = 0; i < N; ++i) tri_id[i] = tri_pos[i] = i;
   int q_base = 0, topology = 1;
   std::vector<Node4Rec> wide;
+  std::vector<Node8Rec> wide8;
   int wide_tri = 0, obj_root4 = -1; // records of the triangle twin (root = record 0); root of the object-tree twin
   const int num_nodes_q = (int)nodes.size();
   if (!(flags & RT_SCENE_REFERENCE_TOPOLOGY) && N > 2 && !root_is_leaf) {
@@ -429,6 +434,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
       if (sah_depth > max_depth) max_depth = sah_depth;
       mark("sah records + reorder");
       wide_tri = collapse_wide(sn, wide) == 0 ? (int)wide.size() : 0;
+      if (wide_tri > 0 && collapse_wide(sn, wide8) != 0) wide8.clear();
       mark("collapse_wide");
       q_base = (int)trav.size();
       topology = 0;
@@ -604,6 +610,8 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   h.off_obj_order = off; off = align_up(off + obj_order.size() * sizeof(int32_t), kSectionAlign);
   h.off_lin_idx = off; off = align_up(off + lin_idx.size() * sizeof(int32_t), kSectionAlign);
   h.off_nodes4 = off;  off = align_up(off + wide.size() * sizeof(Node4Rec), kSectionAlign);
+  h.off_nodes8 = off;  off = align_up(off + wide8.size() * sizeof(Node8Rec), kSectionAlign);
+  h.num_nodes8 = (int)wide8.size();
   h.num_nodes4 = (int)wide.size();
   h.num_nodes4_tri = wide_tri; h.obj_root4 = obj_root4;
   h.obj_root = obj_root; h.num_nodes_obj = num_nodes_obj; h.num_obj_tree = (int)obj_order.size(); h.num_lin = (int)lin_idx.size();
@@ -628,6 +636,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
   if (!obj_order.empty()) std::memcpy(blob.data() + h.off_obj_order, obj_order.data(), obj_order.size() * sizeof(int32_t));
   if (!lin_idx.empty()) std::memcpy(blob.data() + h.off_lin_idx, lin_idx.data(), lin_idx.size() * sizeof(int32_t));
   if (!wide.empty()) parallel_copy(blob.data() + h.off_nodes4, wide.data(), wide.size() * sizeof(Node4Rec));
+  if (!wide8.empty()) parallel_copy(blob.data() + h.off_nodes8, wide8.data(), wide8.size() * sizeof(Node8Rec));
   float *tx = reinterpret_cast<float *>(blob.data() + h.off_texels);
   parallel_ranges(num_texels, 1 << 18, [&](size_t b, size_t e_) {
     for (size_t t = b; t < e_; ++t) {
@@ -648,7 +657,8 @@ int check_blob_header(const BlobHeader &h, size_t bytes, std::string &err) {
   if (!counts_ok) { err = "blob: negative record count"; return RT_ERR_BAD_SCENE; }
   // every section: inside the blob, aligned for its record type, and in the flattener's order (no overlap)
   const uint64_t offs[] = {h.off_nodes, h.off_filter, h.off_exact, h.off_shade, h.off_meshes, h.off_objects, h.off_texels,
-                           h.off_maxx, h.off_tri_id, h.off_tri_pos, h.off_objfilt, h.off_obj_order, h.off_lin_idx, h.off_nodes4};
+                           h.off_maxx, h.off_tri_id, h.off_tri_pos, h.off_objfilt, h.off_obj_order, h.off_lin_idx, h.off_nodes4,
+                           h.off_nodes8};
   for (uint64_t o : offs)
     if (o < sizeof(BlobHeader) || o > bytes || o % 32 != 0) { err = "blob: section offset outside the blob or misaligned"; return RT_ERR_BAD_SCENE; }
   const bool ok = h.off_nodes + (size_t)h.num_nodes * sizeof(NodeRec) <= h.off_filter &&
@@ -666,7 +676,8 @@ int check_blob_header(const BlobHeader &h, size_t bytes, std::string &err) {
                   h.off_lin_idx + (size_t)h.num_lin * sizeof(int32_t) <= h.off_nodes4 &&
                   h.num_nodes4_tri <= h.num_nodes4 &&
                   h.obj_root4 >= -1 && h.obj_root4 < (h.num_nodes4 > 0 ? h.num_nodes4 : 1) &&
-                  h.off_nodes4 + (size_t)h.num_nodes4 * sizeof(Node4Rec) <= h.total_bytes &&
+                  h.off_nodes4 + (size_t)h.num_nodes4 * sizeof(Node4Rec) <= h.off_nodes8 && h.num_nodes8 >= 0 &&
+                  h.off_nodes8 + (size_t)h.num_nodes8 * sizeof(Node8Rec) <= h.total_bytes &&
                   h.num_obj_tree + h.num_lin == h.num_objects &&
                   (h.obj_root < 0 ? h.num_nodes_obj == 0 : h.obj_root == h.q_base + h.num_nodes_q) &&
                   (size_t)h.q_base + (size_t)h.num_nodes_q + (size_t)h.num_nodes_obj == (size_t)h.num_nodes;
@@ -699,6 +710,8 @@ SceneView view_of_blob(const unsigned char *blob) {
   v.num_nodes4 = h.num_nodes4;
   v.obj_root4 = h.obj_root4; v.num_nodes4_tri = h.num_nodes4_tri;
   v.nodes4 = h.num_nodes4 > 0 ? reinterpret_cast<const Node4Rec *>(blob + h.off_nodes4) : nullptr;
+  v.nodes8 = h.num_nodes8 > 0 ? reinterpret_cast<const Node8Rec *>(blob + h.off_nodes8) : nullptr;
+  v.num_nodes8 = h.num_nodes8;
   v.texels = reinterpret_cast<const float *>(blob + h.off_texels);
   v.tex_objs = nullptr;
   v.maxx = reinterpret_cast<const NodeMaxX *>(blob + h.off_maxx);

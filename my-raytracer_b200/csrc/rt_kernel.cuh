@@ -170,7 +170,12 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     // work on rays of different generations, the node loads stop coalescing and the shading code runs at
     // low lane counts — 10.8-17 ms instead of 7.2, profiles/r01_variants.md.)
     for (;;) {
-      if (COUNT & K_WIDE) {
+      if (COUNT & K_WIDE8) {
+        // ordinary rays walk the 8-wide tree: 6 dependent steps per ray instead of 10, eight independent box tests in each
+        while (__any_sync(kFullMask, H.node >= 0)) {
+          if (H.node >= 0) trav_step8<COUNT>(c, H, C, stk);
+        }
+      } else if (COUNT & K_WIDE) {
         // ordinary rays walk the 4-wide tree: half the dependent steps, four independent box tests in each
         while (__any_sync(kFullMask, H.node >= 0)) {
           if (H.node >= 0) trav_step4<COUNT>(c, H, C, stk);

@@ -41,7 +41,7 @@
 namespace rtb {
 
 constexpr uint32_t kBlobMagic = 0x42325452u; // "RT2B"
-constexpr uint32_t kBlobVersion = 11;
+constexpr uint32_t kBlobVersion = 12;
 constexpr int kStackMax = 64;       // traversal stack entries (reference: int stack[64], mytracer_gpu.cu:348)
 constexpr int kTileW = 8, kTileH = 4; // one warp-sized pixel tile
 constexpr size_t kSectionAlign = 512;
@@ -75,6 +75,18 @@ struct alignas(32) Node4Rec {
   int32_t cnt[4];   // cnt  > 0: leaf child with triangle positions [ref, ref + cnt)
 };
 static_assert(sizeof(Node4Rec) == 128, "Node4Rec must be 128 bytes");
+
+// 256 B (8 x 32-byte loads): one record per node of the 8-wide twin of the triangle traversal tree, collapsed from the same
+// binary SAH tree as Node4Rec (rt_flatten.cpp collapse_wide): eight child boxes as four FFMA2 pairs.  One visit = one
+// dependent load + eight independent slab tests: 6 instead of 10 dependent load -> test -> vote chains per ray on the
+// Office scene for 1.4x the box tests (render_kernel<K_WIDE8>, rt_core.cuh trav_step8).  Triangle tree only: scenes with a
+// tree over analytic spheres keep the 4-wide records.
+struct alignas(32) Node8Rec {
+  float box[4][6][2]; // [pair][ctr.x ctr.y ctr.z half.x half.y half.z][child a, child b]; child k = 2*pair + (a: 0, b: 1)
+  int32_t ref[8];     // cnt == 0: Node8Rec index of an interior child (-1: empty slot)
+  int32_t cnt[8];     // cnt  > 0: leaf child with triangle positions [ref, ref + cnt)
+};
+static_assert(sizeof(Node8Rec) == 256, "Node8Rec must be 256 bytes");
 
 struct alignas(16) TriFilter {
   float p2[3], k_bary; // vertex p2 ; 8u*max(|e1|,|e2|)   (bound on the U,V numerators, per unit rho)
@@ -165,6 +177,9 @@ struct BlobHeader {
   int32_t num_nodes4_tri; // 0: the triangle tree has no 4-wide twin
   int32_t obj_root4;      // -1: the object tree has none
   int32_t pad_h[2];
+  uint64_t off_nodes8;    // Node8Rec[num_nodes8]: the 8-wide twin of the triangle traversal tree (root = record 0)
+  int32_t num_nodes8;     // 0: none
+  int32_t pad_8;
 };
 static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignment");
 
@@ -172,6 +187,8 @@ static_assert(sizeof(BlobHeader) % 16 == 0, "BlobHeader must keep 16-byte alignm
 struct SceneView {
   const NodeRec *nodes;
   const Node4Rec *nodes4;   // 4-wide twin of the traversal tree [0, q_base), or nullptr
+  const Node8Rec *nodes8;   // 8-wide twin of the triangle traversal tree, or nullptr
+  int32_t num_nodes8;
   const TriFilter *filt;
   const TriExact *exact;
   const TriShade *shade;
@@ -205,6 +222,9 @@ inline bool wide_usable(const SceneView &v) {
   return v.num_nodes4 > 0 && tri_ok && obj_ok;
 }
 
+// render_kernel<K_WIDE8>: a triangle tree with an 8-wide twin and no object tree
+inline bool wide8_usable(const SceneView &v) { return v.num_nodes8 > 0 && v.nodes8 != nullptr && v.obj_root < 0 && wide_usable(v); }
+
 struct CameraRec {
   double eye[3], x_dir[3], y_dir[3], lower_left[3];
   int32_t width, height;
@@ -233,7 +253,7 @@ struct FrameOut {
 // indices into the counters array (RT_FLAG_COUNTERS build)
 enum Counter {
   C_RAY_PRIMARY = 0, C_RAY_SHADOW, C_RAY_REFLECT, C_BOX, C_TRI_FILTER, C_TRI_EXACT, C_OBJECT,
-  C_SHADED, C_TEXEL, C_NODES, C_SHADOW_TRIVIAL, C_SHADOW_OCCLUDED, C_NODES4, C_COUNT
+  C_SHADED, C_TEXEL, C_NODES, C_SHADOW_TRIVIAL, C_SHADOW_OCCLUDED, C_NODES4, C_NODES8, C_COUNT
 };
 
 } // namespace rtb

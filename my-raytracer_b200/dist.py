@@ -184,7 +184,11 @@ class FramePipeline:
         import ctypes as C
         from . import capi
         self.C, self.capi, self.lib = C, capi, lib
-        self.scene, self.host, self.dev = scene_handle, host_scene, device
+        # scene_handle may be a LIST of handles of identical copies of the scene: frame f renders copy f % len, so that a
+        # copy is next touched len - 1 frames later (with copies adding up to more than the L2, every frame starts
+        # with its scene out of cache - "inputs larger than L2" instead of an evicting fill)
+        self.scenes = list(scene_handle) if isinstance(scene_handle, (list, tuple)) else [scene_handle]
+        self.scene, self.host, self.dev = self.scenes[0], host_scene, device
         self.W, self.H = width, height
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
@@ -245,7 +249,8 @@ class FramePipeline:
         # ctas_per_sm > 0: every frame's persistent grid takes only that many CTA slots per SM, so the frames in
         # flight run side by side (rt_scene_set_launch_width)
         self.ctas_per_sm = int(ctas_per_sm)
-        capi.check(lib.rt_scene_set_launch_width(scene_handle, self.ctas_per_sm), lib)
+        for h in self.scenes:
+            capi.check(lib.rt_scene_set_launch_width(h, self.ctas_per_sm), lib)
 
     # -- one frame --------------------------------------------------------------------------------
     def submit(self, host_io=False):
@@ -283,7 +288,7 @@ class FramePipeline:
             # into the host frame all ranks share (mapped pinned memory, each rank over its own PCIe link)
             base = self.shared_host.dev_ptr if zero_copy else self.fb_ptr
             fo = capi.FrameOut(base + slot * self.frame_bytes, None, None, None)
-            capi.check(lib.rt_render_device(self.scene, C.byref(self.host.camera), self.d_lpos.data_ptr(),
+            capi.check(lib.rt_render_device(self.scenes[f % len(self.scenes)], C.byref(self.host.camera), self.d_lpos.data_ptr(),
                                             self.d_lcol.data_ptr(), self.nl, C.byref(self.params[slot]), C.byref(fo),
                                             C.c_void_p(cs.cuda_stream)), lib)
             done = torch.cuda.Event()
@@ -329,7 +334,8 @@ class FramePipeline:
 
     def close(self):
         self.drain()
-        self.lib.rt_scene_set_launch_width(self.scene, 0)
+        for h in self.scenes:
+            self.lib.rt_scene_set_launch_width(h, 0)
         self.fb_view = self.ctr_view = None
         for p in self._opened:
             self.lib.rt_ipc_close(p)

@@ -88,7 +88,14 @@ int sim_render(const unsigned char *blob, size_t bytes, const rt_camera *cam, co
       // the same choice of kernel variant as rt_api.cu launch(): the 4-wide twins when every tree of the scene has one
       // and the frame does not ask for the binary records
       const bool wide = wide_usable(ct.sv) && !(ct.fp.flags & RT_FLAG_BINARY_NODES);
-      if (wide) {
+      const bool wide8 = wide && (ct.fp.flags & RT_FLAG_NODES8) && wide8_usable(ct.sv);
+      if (wide8) {
+        begin_pixel<K_COUNT | K_WIDE | K_WIDE8>(ct, H, Cd, px, py);
+        while (H.mode != M_IDLE) {
+          if (H.node != -1) traverse<K_COUNT | K_WIDE | K_WIDE8>(ct, H, Cd, stk);
+          else advance<K_COUNT | K_WIDE | K_WIDE8>(ct, H, Cd);
+        }
+      } else if (wide) {
         begin_pixel<K_COUNT | K_OBJ | K_WIDE>(ct, H, Cd, px, py);
         while (H.mode != M_IDLE) {
           if (H.node != -1) traverse<K_COUNT | K_OBJ | K_WIDE>(ct, H, Cd, stk);

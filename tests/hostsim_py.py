@@ -71,7 +71,8 @@ def render(host, blob=None, flags=0, spp_grid=1, tile=(0, 1, 1), want_ids=True, 
     if st != 0:
         raise RuntimeError("sim_render status %d: %s" % (st, L.sim_last_error().decode()))
     names = ("rays_primary", "rays_shadow", "rays_reflect", "box_tests", "tri_filter", "tri_exact", "object_tests",
-             "shaded_hits", "texel_fetches", "nodes_visited", "shadow_trivial", "shadow_occluded", "nodes4_visited")
+             "shaded_hits", "texel_fetches", "nodes_visited", "shadow_trivial", "shadow_occluded", "nodes4_visited",
+             "nodes8_visited")
     out = dict(rgba8=rgba, pixels=px, hit_id=ids, hit_t=t, counters=dict(zip(names, [int(c) for c in cnt])))
     if cost:
         out["cost_nodes"], out["cost_tris"] = cost_n, cost_t

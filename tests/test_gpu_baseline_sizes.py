@@ -215,3 +215,28 @@ def test_wavefront_pipeline_is_bit_identical_to_the_persistent_kernel(rt, lib, g
     # frames the wavefront does not cover fall back to the persistent kernel
     dev.render(*args, host.params(spp_grid=spp, tile=tile, flags=gpu.RT_FLAG_WAVEFRONT | gpu.RT_FLAG_COUNTERS), want=("rgba8",))
     assert dev.last_pipeline() == "megakernel"
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("office", dict(width=642, height=363)),
+    ("rings", dict(width=210, height=150, nu=96, nv=24)),
+    ("textured", dict(width=256, height=144, tex_size=256, slices=64, stacks=32)),
+    ("scatter", dict(width=256, height=144, n_objects=300)),
+])
+def test_eight_wide_tree_on_the_gpu(rt, lib, gpu, name, kw):
+    """render_kernel<K_WIDE | K_WIDE8> (RT_FLAG_NODES8) against the 4-wide default, plain and instrumented: the same frame
+    bit for bit, the same rays, fewer node visits."""
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    dev = rt.DeviceScene(host)
+    assert dev.info()["num_nodes_wide8"] > 0
+    args = (host.camera, host.lights_pos, host.lights_color)
+    w4 = dev.render(*args, host.params(flags=gpu.RT_FLAG_COUNTERS))
+    w8 = dev.render(*args, host.params(flags=gpu.RT_FLAG_NODES8))
+    w8c = dev.render(*args, host.params(flags=gpu.RT_FLAG_NODES8 | gpu.RT_FLAG_COUNTERS))
+    for other in (w8, w8c):
+        for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+            assert np.array_equal(w4[k], other[k]), k
+    a, b = w4["counters"], w8c["counters"]
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
+        assert a[k] == b[k], k
+    assert b["nodes8_visited"] > 0 and b["nodes_visited"] < 0.8 * a["nodes_visited"]

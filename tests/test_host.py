@@ -222,7 +222,7 @@ def test_wide_tree_structure(rt, lib, sim):
     blob = sim.flatten(host)
     h = _blob_sections(blob)
     N = 34000
-    assert h["version"] == 11 and h["num_nodes4"] > 0 and h["off_nodes4"] % 32 == 0
+    assert h["version"] == 12 and h["num_nodes4"] > 0 and h["off_nodes4"] % 32 == 0
     assert h["off_nodes4"] + 128 * h["num_nodes4"] <= h["total"]
     assert h["num_nodes4"] < 0.6 * h["q_base"]                       # at least ~2 binary records per wide record
     rec = np.frombuffer(blob, np.float32, h["num_nodes4"] * 32, h["off_nodes4"]).reshape(-1, 32)
@@ -327,7 +327,7 @@ def test_tile_sharding_partitions_the_image(rt, lib, sim):
 
 
 def test_blob_header_mirror_and_frame_inputs(rt, lib, sim):
-    """blobfmt.BlobHeader == csrc/rt_types.h BlobHeader (240 bytes, same offsets): magic, version, byte count and an
+    """blobfmt.BlobHeader == csrc/rt_types.h BlobHeader (256 bytes, same offsets): magic, version, byte count and an
     ascending 512-byte-aligned section table on a blob the flattener made; FrameInputs (what a rank that did not build
     the scene submits frames with) carries the same camera, lights and render parameters as the HostScene."""
     from my_raytracer_b200 import blobfmt
@@ -336,10 +336,10 @@ def test_blob_header_mirror_and_frame_inputs(rt, lib, sim):
     host = rt.HostScene(desc, lib)
     blob = sim.flatten(host)
     h = blobfmt.header(blob)
-    assert C.sizeof(blobfmt.BlobHeader) == 240
+    assert C.sizeof(blobfmt.BlobHeader) == 256
     assert h["magic"] == blobfmt.BLOB_MAGIC and h["version"] == blobfmt.BLOB_VERSION and h["total_bytes"] == len(blob)
     offs = [h[k] for k in ("off_nodes", "off_filter", "off_exact", "off_shade", "off_meshes", "off_objects", "off_texels",
-                           "off_maxx", "off_tri_id", "off_tri_pos", "off_objfilt", "off_obj_order", "off_lin_idx", "off_nodes4")]
+                           "off_maxx", "off_tri_id", "off_tri_pos", "off_objfilt", "off_obj_order", "off_lin_idx", "off_nodes4", "off_nodes8")]
     assert offs == sorted(offs) and all(o % 512 == 0 and o <= len(blob) for o in offs)
     assert h["num_tris"] == host.num_triangles and h["num_objects"] == host.num_objects
     fi = rdist.FrameInputs(desc, lib)

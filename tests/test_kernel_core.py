@@ -336,3 +336,29 @@ def test_wavefront_schedule_renders_the_same_frame(rt, lib, sim, name, kw, spp, 
     for k in ("rgba8", "pixels", "hit_id", "hit_t"):
         assert np.array_equal(a[k], b[k]), k
     assert a["counters"] == b["counters"]
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("office", dict(width=240, height=135)),
+    ("rings", dict(width=140, height=100)),
+    ("textured", dict(width=128, height=72, tex_size=64)),
+    ("scatter", dict(width=128, height=72, n_objects=200)),           # d.x == 0 rays stay on the reference tree
+    ("mixed_small", dict(width=120, height=90)),                       # analytic objects tested linearly + meshes
+])
+def test_eight_wide_tree_gives_the_same_frame_in_fewer_steps(rt, lib, sim, name, kw):
+    """The 8-wide twin of the triangle tree (Node8Rec, trav_step8, RT_FLAG_NODES8) against the 4-wide one it shares its
+    binary SAH tree with: bit-identical pixels, ids and ray parameters, the same rays, at most 70 % of the node visits."""
+    from my_raytracer_b200 import blobfmt, capi
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    blob = sim.flatten(host)
+    h = blobfmt.header(blob)
+    assert 0 < h["num_nodes8"] < h["num_nodes4"] and h["off_nodes8"] % 32 == 0
+    a = sim.render(host, blob)
+    b = sim.render(host, blob, flags=capi.RT_FLAG_NODES8)
+    for k in ("rgba8", "pixels", "hit_id", "hit_t"):
+        assert np.array_equal(a[k], b[k]), k
+    ca, cb = a["counters"], b["counters"]
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
+        assert ca[k] == cb[k], k
+    assert cb["nodes8_visited"] > 0 and ca["nodes8_visited"] == 0
+    assert cb["nodes_visited"] < 0.8 * ca["nodes_visited"]
