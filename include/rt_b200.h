@@ -181,6 +181,9 @@ typedef struct rt_scene_info {
   int num_nodes_traversal; /* records of the tree ordinary rays walk */
   int num_nodes_wide;      /* 128-byte four-child records of the 4-wide twins of the traversal trees (0: none) */
   int num_nodes_wide8;     /* 256-byte eight-child records of the triangle tree's 8-wide twin (0: none) */
+  int sah_builder;         /* traversal tree built by: 0 none (reference topology / tiny mesh), 1 host threads, 2 the GPU */
+  double sah_build_ms;     /* wall time of that build inside flatten_ms (GPU: including its transfers) */
+  double sah_device_ms;    /* GPU builder: CUDA-event time of its kernels */
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene;
@@ -204,6 +207,10 @@ int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const 
  * (mybvh.cpp:99-135) rejects boxes through a 0/0 there.  RT_SCENE_REFERENCE_TOPOLOGY keeps every ray on the
  * reference's median-split topology (mybvh.cpp:438-472). */
 #define RT_SCENE_REFERENCE_TOPOLOGY 1u
+/* The traversal tree is built on the GPU by default (rt_sah_gpu.cu: level-synchronous binned SAH + one thread per small
+ * subtree); RT_SCENE_HOST_SAH builds it with the host threads instead (the test twin; a different but equally valid
+ * tree: frames are bit-identical either way). */
+#define RT_SCENE_HOST_SAH 2u
 int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
                        int num_objects, unsigned scene_flags, rt_scene **out);
 int rt_scene_destroy(rt_scene *scene);

@@ -18,6 +18,7 @@ RT_SPHERE, RT_PLANE = 0, 1
 RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR, RT_FLAG_BINARY_NODES = 1, 2, 4, 8
 RT_FLAG_WAVEFRONT, RT_FLAG_MEGAKERNEL, RT_FLAG_NODES8 = 16, 32, 64
 RT_SCENE_REFERENCE_TOPOLOGY = 1
+RT_SCENE_HOST_SAH = 2
 
 c_int_p = C.POINTER(C.c_int)
 c_double_p = C.POINTER(C.c_double)
@@ -107,7 +108,8 @@ class SceneInfo(C.Structure):
                 ("num_nodes_ref", C.c_int), ("num_nodes_flat", C.c_int), ("max_depth_bvh", C.c_int),
                 ("max_leaf_size", C.c_int), ("blob_bytes", C.c_size_t), ("flatten_ms", C.c_double),
                 ("upload_ms", C.c_double), ("topology", C.c_int), ("num_nodes_traversal", C.c_int),
-                ("num_nodes_wide", C.c_int), ("num_nodes_wide8", C.c_int)]
+                ("num_nodes_wide", C.c_int), ("num_nodes_wide8", C.c_int), ("sah_builder", C.c_int),
+                ("sah_build_ms", C.c_double), ("sah_device_ms", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -7,6 +7,7 @@
 // There is no CPU fallback anywhere in this file.
 #include "../../include/rt_b200.h"
 #include "rt_flatten.h"
+#include "rt_sah.h"
 #include "rt_frame.h"
 #include "rt_kernel.cuh"
 #include "rt_wavefront.cuh"
@@ -547,11 +548,20 @@ int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, con
   if (st != RT_OK) { set_error(err); return st; }
   const auto t0 = std::chrono::steady_clock::now();
   std::vector<unsigned char> blob;
+  // the traversal tree is built on this GPU (rt_sah_gpu.cu) unless RT_SCENE_HOST_SAH / RT_B200_SAH=host asks for the host twin
+  set_sah_device_builder(&build_sah_device);
+  if (const char *e = std::getenv("RT_B200_SAH")) if (std::strcmp(e, "host") == 0) scene_flags |= RT_SCENE_HOST_SAH;
   st = flatten_scene(data, bvh, objects, num_objects, scene_flags, blob, err);
   if (st != RT_OK) { set_error(err); return st; }
   const double flat_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  const FlattenStats fs = last_flatten_stats();
   st = rt_scene_create_from_blob(blob.data(), blob.size(), 0, out);
-  if (st == RT_OK) (*out)->info.flatten_ms = flat_ms;
+  if (st == RT_OK) {
+    (*out)->info.flatten_ms = flat_ms;
+    (*out)->info.sah_builder = fs.sah_builder;
+    (*out)->info.sah_build_ms = fs.sah_ms;
+    (*out)->info.sah_device_ms = fs.sah_device_ms;
+  }
   return st;
 }
 

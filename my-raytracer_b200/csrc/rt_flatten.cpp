@@ -20,6 +20,10 @@
 #include <type_traits>
 
 namespace rtb {
+static SahDeviceFn g_sah_device = nullptr;
+static thread_local FlattenStats g_stats;
+void set_sah_device_builder(SahDeviceFn fn) { g_sah_device = fn; }
+const FlattenStats &last_flatten_stats() { return g_stats; }
 namespace {
 
 // Contiguous ranges of [0, n) on the host threads (the flattener's per-triangle passes and section copies are
@@ -91,6 +95,7 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     }
   }
 
+  g_stats = FlattenStats();
   // RT_FLATTEN_TIMING=1: phase times on stderr (diagnostics)
   const bool timing = std::getenv("RT_FLATTEN_TIMING") != nullptr;
   auto t_last = std::chrono::steady_clock::now();
@@ -398,7 +403,18 @@ int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt
     std::vector<SahNode> sn;
     int sah_depth = 0;
     mark("primitive boxes");
-    build_sah(plo.data(), phi.data(), N, order, sn, sah_depth);
+    {
+      const auto tb = std::chrono::steady_clock::now();
+      bool on_device = false;
+      if (g_sah_device && !(flags & RT_SCENE_HOST_SAH)) {
+        std::string derr;
+        on_device = g_sah_device(plo.data(), phi.data(), N, order, sn, sah_depth, &g_stats.sah_device_ms, derr);
+        if (!on_device && timing) std::fprintf(stderr, "[flatten] device SAH build failed (%s): host builder\n", derr.c_str());
+      }
+      if (!on_device) build_sah(plo.data(), phi.data(), N, order, sn, sah_depth);
+      g_stats.sah_builder = on_device ? 2 : 1;
+      g_stats.sah_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tb).count();
+    }
     mark("build_sah");
     if (!sn.empty() && sn[0].count == 0 && sah_depth <= kStackMax) {
       // interior nodes in DFS pre-order, as for the reference tree

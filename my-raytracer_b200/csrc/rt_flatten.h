@@ -12,6 +12,18 @@ namespace rtb {
 int flatten_scene(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
                   int num_objects, unsigned flags, std::vector<unsigned char> &blob, std::string &err);
 
+// Device builder of the traversal tree (rt_sah.h build_sah_device), installed by the CUDA library; host-only builds
+// (tests/hostsim) leave it null and flatten with the host builder.  RT_SCENE_HOST_SAH keeps the host builder.
+using SahDeviceFn = bool (*)(const float *, const float *, int, std::vector<int> &, std::vector<struct SahNode> &, int &,
+                             double *, std::string &);
+void set_sah_device_builder(SahDeviceFn fn);
+struct FlattenStats {
+  int sah_builder = 0;      // 0: no SAH tree built, 1: host builder, 2: device builder
+  double sah_ms = 0.0;      // wall time of the tree build (device: including its transfers)
+  double sah_device_ms = 0.0;
+};
+const FlattenStats &last_flatten_stats();   // of the calling thread's last flatten_scene
+
 // Validates a blob received from another rank (magic, version, section bounds).
 int check_blob(const unsigned char *blob, size_t bytes, std::string &err);
 // The same on a header already copied out of the blob (host or device resident).

@@ -10,6 +10,7 @@
 #ifndef RTB_SAH_H
 #define RTB_SAH_H
 #include <cstdint>
+#include <string>
 #include <vector>
 
 namespace rtb {
@@ -25,6 +26,12 @@ struct SahNode {
 // input (the worker threads only split disjoint subtrees).
 void build_sah(const float *lo, const float *hi, int n, std::vector<int> &order, std::vector<SahNode> &nodes,
                int &depth);
+
+// The same build on the GPU (rt_sah_gpu.cu; not part of host-only builds): level-synchronous binned SAH above 16
+// primitives, one thread per subtree with the exact sweep below.  Same contract; `nodes` may contain unused slots.
+// Returns false with `err` set if the device build could not run (the caller falls back to build_sah).
+bool build_sah_device(const float *lo, const float *hi, int n, std::vector<int> &order, std::vector<SahNode> &nodes,
+                      int &depth, double *device_ms, std::string &err);
 
 } // namespace rtb
 #endif

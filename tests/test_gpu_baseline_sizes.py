@@ -240,3 +240,39 @@ def test_eight_wide_tree_on_the_gpu(rt, lib, gpu, name, kw):
     for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
         assert a[k] == b[k], k
     assert b["nodes8_visited"] > 0 and b["nodes_visited"] < 0.8 * a["nodes_visited"]
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("office", dict(width=480, height=270)),
+    ("rings", dict(width=210, height=150)),
+    ("textured", dict(width=256, height=144, tex_size=256)),
+    ("scatter", dict(width=256, height=144, n_objects=300)),
+    ("mixed_small", dict(width=160, height=120)),
+    ("spheres", dict(width=64, height=64)),                    # no triangles: no tree to build
+])
+def test_gpu_sah_builder_against_the_host_builder(rt, lib, gpu, name, kw):
+    """The traversal tree built on the GPU (rt_sah_gpu.cu, default) against the host builder (RT_SCENE_HOST_SAH): a
+    different tree, the same frame bit for bit (ids, ray parameters, FP64 pixels), comparable quality (node visits and
+    triangle tests within 15 %), and a reproducible blob (two device builds are byte-identical)."""
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    dev = rt.DeviceScene(host)
+    ref = rt.DeviceScene(host, scene_flags=gpu.RT_SCENE_HOST_SAH)
+    tris = host.num_triangles
+    assert dev.info()["sah_builder"] == (2 if tris > 2 else 0) and ref.info()["sah_builder"] == (1 if tris > 2 else 0)
+    args = (host.camera, host.lights_pos, host.lights_color)
+    a = dev.render(*args, host.params(flags=gpu.RT_FLAG_COUNTERS))
+    b = ref.render(*args, host.params(flags=gpu.RT_FLAG_COUNTERS))
+    for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+        assert np.array_equal(a[k], b[k]), k
+    ca, cb = a["counters"], b["counters"]
+    for k in ("rays_primary", "rays_shadow", "rays_reflect", "shaded_hits", "shadow_occluded"):
+        assert ca[k] == cb[k], k
+    if tris > 2:
+        assert ca["nodes_visited"] < 1.15 * cb["nodes_visited"] and ca["tri_filter"] < 1.15 * cb["tri_filter"]
+        again = rt.DeviceScene(host)
+        assert again.export_blob() == dev.export_blob()
+        # the 8-wide twin and the binary records of the GPU-built tree render the same frame too
+        for fl in (gpu.RT_FLAG_NODES8, gpu.RT_FLAG_BINARY_NODES, gpu.RT_FLAG_EXACT_ONLY):
+            c = dev.render(*args, host.params(flags=fl))
+            for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+                assert np.array_equal(a[k], c[k]), (fl, k)
