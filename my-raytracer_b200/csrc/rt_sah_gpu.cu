@@ -538,7 +538,7 @@ bool build_sah_device(const float *h_lo, const float *h_hi, int n, std::vector<i
       if (level > 4096) { err = "build_sah_device: too many levels"; goto fail; }
     }
     if (nsmall > 0)
-      small_subtree_kernel<<<blocks(nsmall), 128>>>(d_small, nsmall, d_lo, d_hi, d_cen, d_order[cur], d_nodes, d_depth);
+      small_subtree_kernel<<<(unsigned)((nsmall + 127) / 128), 128>>>(d_small, nsmall, d_lo, d_hi, d_cen, d_order[cur], d_nodes, d_depth);
     SAHG(cudaGetLastError());
     SAHG(cudaEventRecord(e1));
     SAHG(cudaEventSynchronize(e1));
