@@ -28,10 +28,22 @@
 namespace rtb {
 namespace {
 
-constexpr int kBinsG = 16;
-constexpr int kSmallG = 16;        // subtrees of at most this many primitives: one thread, exact sweep (phase B)
-constexpr int kLeafMaxG = 4;       // rt_sah.cpp kLeafMax
-constexpr float kTravG = 1.2f;     // rt_sah.cpp kTrav
+#ifndef RT_SAHG_BINS
+#define RT_SAHG_BINS 16
+#endif
+#ifndef RT_SAHG_SMALL
+#define RT_SAHG_SMALL 16
+#endif
+#ifndef RT_SAHG_LEAFMAX
+#define RT_SAHG_LEAFMAX 4
+#endif
+#ifndef RT_SAHG_TRAV
+#define RT_SAHG_TRAV 1.2f
+#endif
+constexpr int kBinsG = RT_SAHG_BINS;
+constexpr int kSmallG = RT_SAHG_SMALL;     // subtrees of at most this many primitives: one thread, exact sweep (phase B)
+constexpr int kLeafMaxG = RT_SAHG_LEAFMAX; // rt_sah.cpp kLeafMax
+constexpr float kTravG = RT_SAHG_TRAV;     // rt_sah.cpp kTrav
 constexpr int kDepthSwitchG = 36;  // rt_sah.cpp kDepthSwitch: plain halving below, so the depth fits the traversal stack
 constexpr int kBinWords = 7;       // count, lo[3], hi[3] (floats as order-preserving unsigned)
 constexpr int kNodeBinWords = 3 * kBinsG * kBinWords;
