@@ -7,8 +7,8 @@
 // to produce a good one, deterministically:
 //
 //   phase A  level-synchronous binned SAH for nodes of more than kSmall primitives.  Per level: one binning pass over
-//            the primitives (16 bins x 3 axes per node: count + box; integer min/max/add atomics only, privatised in
-//            shared memory while a thread block lies inside one node), one thread per node evaluates the 45 planes from
+//            the primitives (20 bins x 3 axes per node: count + box; integer min/max/add atomics only, privatised in
+//            shared memory while a thread block lies inside one node), one thread per node evaluates the 57 planes from
 //            the bins and picks the cheapest, a scan over the left/right flags gives every primitive its stable
 //            destination, the scatter also reduces the children's centroid bounds.  Children are numbered by exclusive
 //            scans over the level's nodes, so node numbers and the permutation do not depend on thread timing.
@@ -29,7 +29,7 @@ namespace rtb {
 namespace {
 
 #ifndef RT_SAHG_BINS
-#define RT_SAHG_BINS 16
+#define RT_SAHG_BINS 20
 #endif
 #ifndef RT_SAHG_SMALL
 #define RT_SAHG_SMALL 16
