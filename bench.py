@@ -581,6 +581,35 @@ def run_b200(args):
                   "note": "RT_FLAG_NODES8 (256-byte eight-child records), same frame bit for bit; compare with "
                           "latency_ms_single_frame / roofline.frac_single_frame"}
 
+    # ---- A/B: the traversal tree built by the host threads (round 1's builder) instead of the GPU builder --------------
+    host_tree = None
+    if world == 1 and not args.no_ab and not big and info.get("sah_builder", 0) == 2:
+        sc3 = rt.DeviceScene(host, scene_flags=scene_flags | capi.RT_SCENE_HOST_SAH)
+        ms4 = []
+        for i in range(8):
+            evict()
+            capi.check(lib.rt_render_device(sc3.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
+                                            C.byref(sparams), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
+            ms4.append(sc3.last_kernel_ms())
+        k4 = sum(ms4[2:]) / len(ms4[2:])
+        hp = host.params(spp_grid=spp_grid, tile=pipe.tile, flags=capi.RT_FLAG_COUNTERS)
+        capi.check(lib.rt_render_device(sc3.handle, C.byref(cam), pipe.d_lpos.data_ptr(), pipe.d_lcol.data_ptr(), nl,
+                                        C.byref(hp), C.byref(fo), C.c_void_p(stream.cuda_stream)), lib)
+        c4 = capi.Counters()
+        capi.check(lib.rt_get_counters(sc3.handle, C.byref(c4)), lib)
+        c4 = c4.as_dict()
+        f4 = 24 * c4["box_tests"] + 48 * c4["tri_filter"] + (60 * nl + 20) * c4["shaded_hits"]
+        i3 = sc3.info()
+        host_tree = {"kernel_ms_single_frame": k4, "mrays": rays_frame / (k4 * 1e-3) / 1e6, "box_tests": c4["box_tests"],
+                     "nodes_visited": c4["nodes_visited"], "flops_per_launch": f4,
+                     "fp32_frac_single_frame": f4 / (k4 * 1e-3) / 1e12 / (148 * 128 * 2 * float(measured_peaks().get("sm_max_mhz", 1965.0)) * 1e6 / 1e12),
+                     "sah_build_ms": i3["sah_build_ms"], "flatten_ms": i3["flatten_ms"],
+                     "note": "RT_SCENE_HOST_SAH: the host builder's tree (32 bins / exact sweep), same frame bit for bit; the GPU "
+                             "builder's tree needs fewer box tests per ray, so the same kernel renders the frame faster at a "
+                             "LOWER fraction of the FP32 roofline (fewer counted flops); compare with latency_ms_single_frame / "
+                             "roofline.frac_single_frame"}
+        sc3.close()
+
     wide = tot.get("nodes4_visited", 0) > 0      # ordinary rays walked the 4-wide tree (render_kernel<K_WIDE>)
     # ---- roofline of the render kernel -------------------------------------------------------------
     peaks = measured_peaks()
@@ -652,6 +681,7 @@ def run_b200(args):
             "other_tree": other_tree,
             "binary_nodes": binary_nodes,
             "nodes8": nodes8,
+            "host_sah_tree": host_tree,
             "flush_ab": flush_ab,
             "rays_per_frame": {k: tot[k] for k in ("rays_primary", "rays_shadow", "rays_reflect")},
             "counters": tot,
@@ -662,6 +692,8 @@ def run_b200(args):
             "gpu_launches": args.steps * world * (1 if pipeline_ran == "megakernel" else 2 * (desc.max_depth + 2) * spp_grid * spp_grid),
             "roofline": roof,
             "setup_ms": {"host_scene_build": host_ms, "flatten": info["flatten_ms"], "upload": info["upload_ms"],
+                         "sah_builder": {0: "none", 1: "host threads", 2: "GPU (rt_sah_gpu.cu)"}.get(info.get("sah_builder", 0)),
+                         "sah_build": info.get("sah_build_ms"), "sah_build_device_kernels": info.get("sah_device_ms"),
                          "broadcast": bcast_ms, "blob_bytes": info["blob_bytes"],
                          "broadcast_how": "NCCL from rank 0's resident blob (device to device)" if world > 1 else None},
         }
