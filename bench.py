@@ -312,9 +312,10 @@ def run_b200(args):
     # single heavy tile (8 GPUs: ~0.2 ms of work per GPU), so 8 frames are kept in flight on narrower grids (2 CTAs
     # per SM each at 2-4 GPUs, 1 at 8: frames resident side by side, every warp renders 2-4x more tiles of its
     # frame) - profiles/r01_variants.md.  The 10 M-triangle frame is 20 ms of work: 2 frames in flight suffice.
-    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "2" if big else ("8" if world >= 2 else "4")))
+    # (with 4 in flight and 30 % of the tiles in the cross-GPU dynamic queue its heavy tiles balance: 3.08 -> 2.79 ms at 8 GPUs)
+    depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "4" if big else ("8" if world >= 2 else "4")))
     # the wavefront shards tiles statically only (no cross-GPU dynamic tail)
-    dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", "0.15" if args.pipeline == "megakernel" else "0"))
+    dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", ("0.3" if big else "0.15") if args.pipeline == "megakernel" else "0"))
     pflags = capi.RT_FLAG_WAVEFRONT if args.pipeline == "wavefront" else capi.RT_FLAG_MEGAKERNEL
     FLUSH = int(os.environ.get("RT_FLUSH_MB", "160")) * 1024 * 1024             # > 126 MB L2 (env: experiments only)
     # 0 = full-width grids (one GPU); half-width at 2-4 GPUs; quarter-width at 8
@@ -391,7 +392,11 @@ def run_b200(args):
         return (rdist.max_over_ranks(ms, dev) if world > 1 else ms), slot
 
     # ---- timed region: value (device-resident inputs, frames in flight) --------------------------------------
-    for _ in range(max(args.warmup, 3)):
+    # untimed warm-up: at least W frames, and with the rotating scene copies two rounds over all of them (every copy's
+    # pages, TLB entries and launch resources touched) plus one pipeline depth - the first frames on a fresh process run
+    # up to 10 % slower than the steady state
+    n_warm = max(args.warmup, 3, (2 * ncopies + depth) if (flush_mode == "rotate" and ncopies > 1) else 0)
+    for _ in range(n_warm):
         pipe.submit()
     sampler = ClockSampler(local_rank)
     sampler.sample()
@@ -671,7 +676,7 @@ def run_b200(args):
                               "off": "NOT evicted (experiment)"}[flush_mode],
                        "timing": "steady-state window: value is THROUGHPUT with frames_in_flight frames in flight "
                                  "(one frame alone: latency_ms_single_frame)",
-                       "frames_in_flight": pipe.depth, "ctas_per_sm_per_frame": pipe.ctas_per_sm or "all",
+                       "warmup_frames_run": n_warm, "frames_in_flight": pipe.depth, "ctas_per_sm_per_frame": pipe.ctas_per_sm or "all",
                        "parallelism": f"tiles{world}" if world > 1 else "single",
                        "tile_chunk": pipe.tile[2], "dyn_tiles": pipe.dyn_tiles, "dyn_chunk": pipe.dyn_chunk,
                        "gather": "fused: peer stores into rank 0's frame buffer over NVLink + 4-byte all-reduce signal"

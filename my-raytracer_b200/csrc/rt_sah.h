@@ -30,6 +30,15 @@ void build_sah(const float *lo, const float *hi, int n, std::vector<int> &order,
 // The same build on the GPU (rt_sah_gpu.cu; not part of host-only builds): level-synchronous binned SAH above 16
 // primitives, one thread per subtree with the exact sweep below.  Same contract; `nodes` may contain unused slots.
 // Returns false with `err` set if the device build could not run (the caller falls back to build_sah).
+// The device-resident form: boxes in, tree left in HBM (rt_flatten_gpu.cu emits the blob's records from it).
+struct SahDeviceTree {
+  int *order = nullptr;       // [n] device: primitive of every position
+  SahNode *nodes = nullptr;   // device: phase-A nodes [0, nodes_a), phase-B blocks [cap_a, reserve); unwritten slots: count = -1
+  int n = 0, nodes_a = 0, depth = 0;
+  size_t cap_a = 0, reserve = 0;
+};
+bool build_sah_on_device(const float *d_lo, const float *d_hi, int n, SahDeviceTree &tree, double *device_ms, std::string &err);
+void free_sah_device_tree(SahDeviceTree &tree);
 bool build_sah_device(const float *lo, const float *hi, int n, std::vector<int> &order, std::vector<SahNode> &nodes,
                       int &depth, double *device_ms, std::string &err);
 

@@ -430,13 +430,12 @@ __global__ void small_subtree_kernel(const SmallRoot *__restrict__ roots, int nr
 
 } // namespace
 
-// Device build of the traversal tree.  Same contract as build_sah; `nodes` may contain unused slots (never referenced).
-// Returns false (err set) when the device build is not possible; the caller then uses the host builder.
-bool build_sah_device(const float *h_lo, const float *h_hi, int n, std::vector<int> &order, std::vector<SahNode> &nodes,
-                      int &depth, double *device_ms, std::string &err) {
-  order.clear(); nodes.clear(); depth = 0;
+// The build on primitive boxes that already live on the device; the tree stays there (rt_flatten_gpu.cu emits the
+// records from it).  Slots of t.nodes that the build never wrote hold count = -1 (0xff fill).
+bool build_sah_on_device(const float *d_lo, const float *d_hi, int n, SahDeviceTree &t, double *device_ms, std::string &err) {
+  t = SahDeviceTree();
   if (n <= 0) return true;
-  float *d_lo = nullptr, *d_hi = nullptr, *d_cen = nullptr;
+  float *d_cen = nullptr;
   int *d_order[2] = {nullptr, nullptr}, *d_slot[2] = {nullptr, nullptr}, *d_flags = nullptr, *d_pref = nullptr;
   int *d_fl = nullptr, *d_fs = nullptr, *d_fr = nullptr, *d_il = nullptr, *d_is = nullptr, *d_or = nullptr, *d_cslot = nullptr;
   unsigned *d_bins = nullptr, *d_root = nullptr;
@@ -461,8 +460,6 @@ bool build_sah_device(const float *h_lo, const float *h_hi, int n, std::vector<i
     cub::DeviceScan::ExclusiveSum(nullptr, t2, (int *)nullptr, (int *)nullptr, 2 * max_work);
     tmp_bytes = t1 > t2 ? t1 : t2;
   }
-  SAHG(cudaMalloc(&d_lo, 3 * N * sizeof(float)));
-  SAHG(cudaMalloc(&d_hi, 3 * N * sizeof(float)));
   SAHG(cudaMalloc(&d_cen, 3 * N * sizeof(float)));
   for (int k = 0; k < 2; ++k) {
     SAHG(cudaMalloc(&d_order[k], N * sizeof(int)));
@@ -485,11 +482,10 @@ bool build_sah_device(const float *h_lo, const float *h_hi, int n, std::vector<i
   SAHG(cudaMalloc(&d_split, (size_t)max_work * sizeof(Split)));
   SAHG(cudaMalloc(&d_small, (N + 2) * sizeof(SmallRoot)));
   SAHG(cudaMalloc(&d_nodes, cap_nodes * sizeof(SahNode)));
+  SAHG(cudaMemset(d_nodes, 0xff, cap_nodes * sizeof(SahNode)));
   SAHG(cudaMalloc(&d_tmp, tmp_bytes ? tmp_bytes : 16));
   SAHG(cudaEventCreate(&e0));
   SAHG(cudaEventCreate(&e1));
-  SAHG(cudaMemcpy(d_lo, h_lo, 3 * N * sizeof(float), cudaMemcpyHostToDevice));
-  SAHG(cudaMemcpy(d_hi, h_hi, 3 * N * sizeof(float), cudaMemcpyHostToDevice));
   SAHG(cudaEventRecord(e0));
   {
     const unsigned init[12] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
@@ -555,26 +551,57 @@ bool build_sah_device(const float *h_lo, const float *h_hi, int n, std::vector<i
     SAHG(cudaEventRecord(e1));
     SAHG(cudaEventSynchronize(e1));
     if (device_ms) { float ms = 0.0f; cudaEventElapsedTime(&ms, e0, e1); *device_ms = ms; }
-    order.resize(N);
-    SAHG(cudaMemcpy(order.data(), d_order[cur], N * sizeof(int), cudaMemcpyDeviceToHost));
-    const size_t used = (size_t)reserve;      // phase-A nodes [0, nodes_a), phase-B blocks [cap_a, reserve)
-    nodes.resize(used);
-    SAHG(cudaMemcpy(nodes.data(), d_nodes, (size_t)nodes_a * sizeof(SahNode), cudaMemcpyDeviceToHost));
-    if (used > cap_a)
-      SAHG(cudaMemcpy(nodes.data() + cap_a, d_nodes + cap_a, (used - cap_a) * sizeof(SahNode), cudaMemcpyDeviceToHost));
     int dd = 0;
     SAHG(cudaMemcpy(&dd, d_depth, sizeof(int), cudaMemcpyDeviceToHost));
-    depth = dd > level ? dd : level;
+    t.order = d_order[cur]; d_order[cur] = nullptr;
+    t.nodes = d_nodes; d_nodes = nullptr;
+    t.n = n; t.nodes_a = nodes_a; t.cap_a = cap_a; t.reserve = (size_t)reserve;
+    t.depth = dd > level ? dd : level;
     ok = true;
   }
 fail:
-  cudaFree(d_lo); cudaFree(d_hi); cudaFree(d_cen);
+  cudaFree(d_cen);
   for (int k = 0; k < 2; ++k) { cudaFree(d_order[k]); cudaFree(d_slot[k]); cudaFree(d_work[k]); }
   cudaFree(d_flags); cudaFree(d_pref); cudaFree(d_fl); cudaFree(d_fs); cudaFree(d_fr); cudaFree(d_il); cudaFree(d_is);
   cudaFree(d_or); cudaFree(d_cslot); cudaFree(d_bins); cudaFree(d_root); cudaFree(d_depth); cudaFree(d_tot); cudaFree(d_split);
   cudaFree(d_small); cudaFree(d_nodes); cudaFree(d_tmp);
   if (e0) cudaEventDestroy(e0);
   if (e1) cudaEventDestroy(e1);
+  if (!ok) cudaGetLastError();
+  return ok;
+}
+
+void free_sah_device_tree(SahDeviceTree &t) {
+  cudaFree(t.order); cudaFree(t.nodes);
+  t = SahDeviceTree();
+}
+
+// Device build of the traversal tree from host boxes.  Same contract as build_sah; `nodes` may contain unused slots (never
+// referenced).  Returns false (err set) when the device build is not possible; the caller then uses the host builder.
+bool build_sah_device(const float *h_lo, const float *h_hi, int n, std::vector<int> &order, std::vector<SahNode> &nodes,
+                      int &depth, double *device_ms, std::string &err) {
+  order.clear(); nodes.clear(); depth = 0;
+  if (n <= 0) return true;
+  float *d_lo = nullptr, *d_hi = nullptr;
+  SahDeviceTree t;
+  const size_t N = (size_t)n;
+  bool ok = false;
+  SAHG(cudaMalloc(&d_lo, 3 * N * sizeof(float)));
+  SAHG(cudaMalloc(&d_hi, 3 * N * sizeof(float)));
+  SAHG(cudaMemcpy(d_lo, h_lo, 3 * N * sizeof(float), cudaMemcpyHostToDevice));
+  SAHG(cudaMemcpy(d_hi, h_hi, 3 * N * sizeof(float), cudaMemcpyHostToDevice));
+  if (!build_sah_on_device(d_lo, d_hi, n, t, device_ms, err)) goto fail;
+  order.resize(N);
+  SAHG(cudaMemcpy(order.data(), t.order, N * sizeof(int), cudaMemcpyDeviceToHost));
+  nodes.resize(t.reserve);      // phase-A nodes [0, nodes_a), phase-B blocks [cap_a, reserve)
+  SAHG(cudaMemcpy(nodes.data(), t.nodes, (size_t)t.nodes_a * sizeof(SahNode), cudaMemcpyDeviceToHost));
+  if (t.reserve > t.cap_a)
+    SAHG(cudaMemcpy(nodes.data() + t.cap_a, t.nodes + t.cap_a, (t.reserve - t.cap_a) * sizeof(SahNode), cudaMemcpyDeviceToHost));
+  depth = t.depth;
+  ok = true;
+fail:
+  cudaFree(d_lo); cudaFree(d_hi);
+  free_sah_device_tree(t);
   if (!ok) { order.clear(); nodes.clear(); depth = 0; cudaGetLastError(); }
   return ok;
 }
