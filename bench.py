@@ -395,7 +395,7 @@ def run_b200(args):
     # untimed warm-up: at least W frames, and with the rotating scene copies two rounds over all of them (every copy's
     # pages, TLB entries and launch resources touched) plus one pipeline depth - the first frames on a fresh process run
     # up to 10 % slower than the steady state
-    n_warm = max(args.warmup, 3, (2 * ncopies + depth) if (flush_mode == "rotate" and ncopies > 1) else 0)
+    n_warm = max(args.warmup, 3, (2 * ncopies + depth) if (flush_mode == "rotate" and ncopies > 1) else (2 * depth + 2))
     for _ in range(n_warm):
         pipe.submit()
     sampler = ClockSampler(local_rank)
