@@ -241,6 +241,22 @@ int rt_render(rt_scene *scene, const rt_camera *camera, const rt_vec4 *lights_po
 int rt_render_device(rt_scene *scene, const rt_camera *camera, const rt_vec4 *d_lights_pos,
                      const rt_vec4 *d_lights_color, int num_lights, const rt_render_params *params,
                      const rt_frame_out *out_device, void *stream);
+/* rt_render_device on memory that is part of the loaded module: allocates NOTHING (no cudaMalloc / cudaFree, no
+ * allocating library routine), for callers that cannot allocate - code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it.  No counterpart in the reference.
+ * Same arguments, arithmetic and (bit-identical) frame as rt_render_device; the frame runs as the wavefront
+ * (RT_FLAG_WAVEFRONT schedule) with its path-state scratch in one file-scope __device__ array of 18.6 MB that every GPU
+ * loading the library holds until the process exits.  LIMITS (RT_ERR_LIMIT with a message beyond them): at most
+ * 65536 path slots = 32 x the 8x4-pixel tiles of this rank's share of the frame (e.g. 256 x 256 pixels; spp_grid does
+ * not count, samples are passes over the same slots), at most 8 lights, max_depth <= 30.  RT_FLAG_COUNTERS and the
+ * dynamic tile queue (dyn_tiles) are refused with RT_ERR_INVALID_ARG.  The scene's device must be current.  All calls of
+ * a process on one GPU share the array, which keeps the last call's contents: two calls that overlap on the GPU
+ * (different streams or host threads) race; order them on one stream or with events.  The first call on a
+ * device looks the array's device address up (cudaGetSymbolAddress); make it before a stream capture begins.  Does not
+ * update rt_last_kernel_ms / rt_last_pipeline. */
+int rt_render_device_static(rt_scene *scene, const rt_camera *camera, const rt_vec4 *d_lights_pos,
+                            const rt_vec4 *d_lights_color, int num_lights, const rt_render_params *params,
+                            const rt_frame_out *out_device, void *stream);
 /* Launches of one scene may be in flight on several streams.  Each takes its work counter and event pair from a
  * ring of 8 slots; launch f + 8 is ordered behind launch f (cudaStreamWaitEvent), so more than 8 frames in flight
  * are safe but serialise.  RT_FLAG_COUNTERS launches are synchronous (the counters are read back before the

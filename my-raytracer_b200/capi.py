@@ -148,6 +148,8 @@ PROTOTYPES = {
                             C.POINTER(FrameOut)]),
     "rt_render_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_int,
                                    C.POINTER(RenderParams), C.POINTER(FrameOut), C.c_void_p]),
+    "rt_render_device_static": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_int,
+                                   C.POINTER(RenderParams), C.POINTER(FrameOut), C.c_void_p]),
     "rt_frame_queue_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(FrameQueueOpts), C.POINTER(C.c_void_p)]),
     "rt_frame_submit": (C.c_int, [C.c_void_p, C.POINTER(Camera), Vec4_p, Vec4_p, C.c_int, C.POINTER(RenderParams),
                                   C.c_void_p, C.POINTER(C.c_longlong)]),

@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -485,6 +486,44 @@ int fetch_counters(rt_scene *s, cudaStream_t st) {
   return RT_OK;
 }
 
+// ---- rt_render_device_static: the wavefront frame on scratch that is part of the loaded module ---------------------
+// The wavefront kernels exchange rays through path-state columns in HBM (rt_wavefront.cuh).  launch_wavefront takes
+// them from cudaMalloc; this variant takes them from ONE file-scope array, so the call allocates nothing.  The array
+// is reserved on every GPU that loads the library, for the life of the process; every call on a device shares it and
+// it keeps the last call's contents (path columns are fully rewritten by bounce 0 of each pass, the control block is
+// cleared in-stream by the call).  Two calls that overlap on one GPU race on it.
+constexpr long long kStaticMaxPaths = 65536;   // work slots of 32-pixel tiles: e.g. 256 x 256 pixels (any spp_grid)
+constexpr int kStaticMaxLights = 8;
+constexpr size_t kStaticOffCtl = 0;                                                           // kWfCtlWords u64
+constexpr size_t kStaticOffWd = 512;                                                          // WD_NUM double columns
+constexpr size_t kStaticOffWi = kStaticOffWd + sizeof(double) * WD_NUM * (size_t)kStaticMaxPaths; // WI_NUM int columns
+constexpr size_t kStaticOffOccl = kStaticOffWi + sizeof(int) * WI_NUM * (size_t)kStaticMaxPaths;  // one byte column per light
+constexpr size_t kStaticBytes = kStaticOffOccl + (size_t)kStaticMaxLights * (size_t)kStaticMaxPaths;
+static_assert(sizeof(unsigned long long) * kWfCtlWords <= kStaticOffWd, "control block");
+static_assert(kStaticOffWd % 256 == 0 && kStaticOffWi % 256 == 0 && kStaticOffOccl % 256 == 0, "column alignment");
+static_assert(kStaticBytes <= (20u << 20), "static scratch is meant to stay modest (about 18.6 MB)");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol: the address a kernel may use is per device and
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kStaticMaxDevices = 64;
+unsigned char *g_static_ptr[kStaticMaxDevices] = {};
+std::mutex g_static_mu;
+
+int static_scratch_ptr(int device, unsigned char **out) {
+  if (device < 0 || device >= kStaticMaxDevices) { set_error("rt_render_device_static: device ordinal out of range"); return RT_ERR_LIMIT; }
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[device]) {
+    unsigned char *p = nullptr;
+    RT_CUDA(cudaGetSymbolAddress((void **)&p, g_static_scratch));
+    if (!p) { set_error("rt_render_device_static: cudaGetSymbolAddress returned a null address"); return RT_ERR_CUDA; }
+    g_static_ptr[device] = p;
+  }
+  *out = g_static_ptr[device];
+  return RT_OK;
+}
+
 } // namespace
 
 extern "C" {
@@ -632,6 +671,79 @@ int rt_render_device(rt_scene *s, const rt_camera *camera, const rt_vec4 *d_ligh
   return fetch_counters(s, stx);
 #endif
   if (fp.flags & RT_FLAG_COUNTERS) return fetch_counters(s, stx);
+  return RT_OK;
+}
+
+// No counterpart in the reference: added for callers that must not allocate
+// (CUDA graph capture, tight serving loops).  Calls no cudaMalloc / cudaFree and touches no per-scene launch state.
+int rt_render_device_static(rt_scene *s, const rt_camera *camera, const rt_vec4 *d_lights_pos,
+                            const rt_vec4 *d_lights_color, int num_lights, const rt_render_params *params,
+                            const rt_frame_out *out, void *stream) {
+  if (!s) { set_error("rt_render_device_static: null scene"); return RT_ERR_INVALID_ARG; }
+  FrameParams fp;
+  std::string err;
+  int st = make_frame_params(camera, num_lights, params, out, fp, err);
+  if (st != RT_OK) { set_error(err); return st; }
+  if (num_lights > 0 && (!d_lights_pos || !d_lights_color)) { set_error("rt_render_device_static: null lights"); return RT_ERR_INVALID_ARG; }
+  if ((fp.flags & RT_FLAG_COUNTERS) || fp.static_tiles != fp.tiles_x * fp.tiles_y) {
+    set_error("rt_render_device_static: RT_FLAG_COUNTERS and the dynamic tile queue are not available on the static-scratch path");
+    return RT_ERR_INVALID_ARG;
+  }
+  Ctx hc;
+  hc.fp = fp; hc.pixel_list = nullptr; hc.list_count = 0;
+  const long long npaths = work_slots(hc);
+  if (npaths > kStaticMaxPaths) {
+    set_error("rt_render_device_static: the frame needs " + std::to_string(npaths) + " path slots (32 per 8x4 tile of this rank's "
+              "share), the static scratch holds " + std::to_string(kStaticMaxPaths) + " (e.g. 256x256 pixels); use rt_render_device");
+    return RT_ERR_LIMIT;
+  }
+  if (num_lights > kStaticMaxLights) {
+    set_error("rt_render_device_static: " + std::to_string(num_lights) + " lights, the static scratch holds shadow results of " +
+              std::to_string(kStaticMaxLights) + "; use rt_render_device");
+    return RT_ERR_LIMIT;
+  }
+  if (fp.max_depth > kWfMaxDepth) { set_error("rt_render_device_static: max_depth above 30"); return RT_ERR_LIMIT; }
+  int cur = -1;
+  RT_CUDA(cudaGetDevice(&cur));
+  if (cur != s->device) { set_error("rt_render_device_static: the scene's device must be the current device"); return RT_ERR_INVALID_ARG; }
+  unsigned char *base = nullptr;
+  st = static_scratch_ptr(cur, &base);
+  if (st != RT_OK) return st;
+  cudaStream_t stx = static_cast<cudaStream_t>(stream);
+  unsigned long long *ctl = reinterpret_cast<unsigned long long *>(base + kStaticOffCtl);
+  WfArgs a;
+  a.sv = s->view; a.fp = fp;
+  a.light_pos = reinterpret_cast<const double *>(d_lights_pos); a.light_col = reinterpret_cast<const double *>(d_lights_color);
+  a.out.rgba8 = out->rgba8; a.out.pixels = reinterpret_cast<double *>(out->pixels);
+  a.out.hit_id = out->hit_id; a.out.hit_t = out->hit_t;
+  a.w.wd = reinterpret_cast<double *>(base + kStaticOffWd);
+  a.w.wi = reinterpret_cast<int *>(base + kStaticOffWi);
+  a.w.occl = base + kStaticOffOccl;
+  a.w.npaths = npaths;
+  a.pending = reinterpret_cast<unsigned int *>(ctl + kWfCtlTasks);
+  a.counters = nullptr;
+  const bool wide = s->wide_ok && !(fp.flags & RT_FLAG_BINARY_NODES);
+  const bool obj = s->hdr.obj_root >= 0;
+  const int cfg = (obj ? 1 : 0) | (wide ? 2 : 0);
+  const int grid = s->grid_wf[cfg];
+  const unsigned sgrid = (unsigned)((npaths + kBlockThreads - 1) / kBlockThreads);
+  const int s2 = fp.spp_grid * fp.spp_grid;
+  for (int sample = 0; sample < s2; ++sample) {
+    // what must start at zero: the task counters and pending[] of this pass (the array keeps the last call's contents)
+    RT_CUDA(cudaMemsetAsync(ctl, 0, sizeof(unsigned long long) * kWfCtlWords, stx));
+    a.sample = sample;
+    for (int b = 0; b <= fp.max_depth + 1; ++b) {
+      a.bounce = b;
+      a.task_counter = ctl + b;
+      switch (cfg) {
+        case 0: wf_trace_kernel<0><<<grid, kBlockThreads, 0, stx>>>(a); wf_shade_kernel<0><<<sgrid, kBlockThreads, 0, stx>>>(a); break;
+        case 1: wf_trace_kernel<K_OBJ><<<grid, kBlockThreads, 0, stx>>>(a); wf_shade_kernel<K_OBJ><<<sgrid, kBlockThreads, 0, stx>>>(a); break;
+        case 2: wf_trace_kernel<K_WIDE><<<grid, kBlockThreads, 0, stx>>>(a); wf_shade_kernel<K_WIDE><<<sgrid, kBlockThreads, 0, stx>>>(a); break;
+        default: wf_trace_kernel<K_WIDE | K_OBJ><<<grid, kBlockThreads, 0, stx>>>(a); wf_shade_kernel<K_WIDE | K_OBJ><<<sgrid, kBlockThreads, 0, stx>>>(a); break;
+      }
+    }
+  }
+  RT_CUDA(cudaGetLastError());
   return RT_OK;
 }
 
