@@ -697,6 +697,7 @@ def run_b200(args):
             "gpu_launches": args.steps * world * (1 if pipeline_ran == "megakernel" else 2 * (desc.max_depth + 2) * spp_grid * spp_grid),
             "roofline": roof,
             "setup_ms": {"host_scene_build": host_ms, "flatten": info["flatten_ms"], "upload": info["upload_ms"],
+                         "flattener": {0: "host threads (rt_flatten.cpp)", 1: "GPU (rt_flatten_gpu.cu)"}.get(info.get("flattener", 0)),
                          "sah_builder": {0: "none", 1: "host threads", 2: "GPU (rt_sah_gpu.cu)"}.get(info.get("sah_builder", 0)),
                          "sah_build": info.get("sah_build_ms"), "sah_build_device_kernels": info.get("sah_device_ms"),
                          "broadcast": bcast_ms, "blob_bytes": info["blob_bytes"],

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 5
+#define RT_B200_ABI_VERSION 6
 
 typedef enum rt_status {
   RT_OK = 0,
@@ -184,6 +184,8 @@ typedef struct rt_scene_info {
   int sah_builder;         /* traversal tree built by: 0 none (reference topology / tiny mesh), 1 host threads, 2 the GPU */
   double sah_build_ms;     /* wall time of that build inside flatten_ms (GPU: including its transfers) */
   double sah_device_ms;    /* GPU builder: CUDA-event time of its kernels */
+  int flattener;           /* records emitted by: 0 the host threads (rt_flatten.cpp), 1 the GPU (rt_flatten_gpu.cu) */
+  int pad_;
 } rt_scene_info;
 
 typedef struct rt_scene rt_scene;
@@ -211,6 +213,12 @@ int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const 
  * subtree); RT_SCENE_HOST_SAH builds it with the host threads instead (the test twin; a different but equally valid
  * tree: frames are bit-identical either way). */
 #define RT_SCENE_HOST_SAH 2u
+/* The blob's records (triangle filter / exact / shading records, the node records of all trees, texels) are emitted on
+ * the GPU from the uploaded Data / BVH arrays by default (rt_flatten_gpu.cu: 10 M triangles in under a second instead
+ * of 7 s on the host threads); RT_SCENE_HOST_FLATTEN (or RT_B200_FLATTEN=host in the environment) keeps the host
+ * flattener, which also handles every scene the device path declines (reference topology, a root that is a leaf,
+ * malformed input: it words the error).  Frames are bit-identical either way; rt_scene_info.flattener says which ran. */
+#define RT_SCENE_HOST_FLATTEN 4u
 int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
                        int num_objects, unsigned scene_flags, rt_scene **out);
 int rt_scene_destroy(rt_scene *scene);

@@ -19,6 +19,7 @@ RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR, RT_FLAG_BINARY_NODES = 1
 RT_FLAG_WAVEFRONT, RT_FLAG_MEGAKERNEL, RT_FLAG_NODES8 = 16, 32, 64
 RT_SCENE_REFERENCE_TOPOLOGY = 1
 RT_SCENE_HOST_SAH = 2
+RT_SCENE_HOST_FLATTEN = 4
 
 c_int_p = C.POINTER(C.c_int)
 c_double_p = C.POINTER(C.c_double)
@@ -109,7 +110,7 @@ class SceneInfo(C.Structure):
                 ("max_leaf_size", C.c_int), ("blob_bytes", C.c_size_t), ("flatten_ms", C.c_double),
                 ("upload_ms", C.c_double), ("topology", C.c_int), ("num_nodes_traversal", C.c_int),
                 ("num_nodes_wide", C.c_int), ("num_nodes_wide8", C.c_int), ("sah_builder", C.c_int),
-                ("sah_build_ms", C.c_double), ("sah_device_ms", C.c_double)]
+                ("sah_build_ms", C.c_double), ("sah_device_ms", C.c_double), ("flattener", C.c_int), ("pad_", C.c_int)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -209,7 +210,7 @@ def load_library(path: str | None = None):
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.rt_abi_version() != 5:
+    if lib.rt_abi_version() != 6:
         raise RuntimeError("rt_b200 ABI version mismatch")
     if path is None:
         _lib = lib

@@ -570,6 +570,26 @@ int rt_scene_create_from_blob(const void *blob, size_t bytes, int is_device, rt_
   return RT_OK;
 }
 
+// Adopts a blob the device flattener built in HBM (no copy); frees it on failure.
+static int scene_from_device_blob(DeviceBlob &db, rt_scene **out) {
+  std::string err;
+  int st = check_blob_header(db.hdr, db.bytes, err);
+  if (st != RT_OK) { cudaFree(db.d_blob); db.d_blob = nullptr; set_error(err); return st; }
+  int device = 0;
+  cudaError_t e = cudaGetDevice(&device);
+  if (e != cudaSuccess) { cudaFree(db.d_blob); db.d_blob = nullptr; set_error("cudaGetDevice failed"); return RT_ERR_CUDA; }
+  rt_scene *s = new rt_scene();
+  s->device = device;
+  s->bytes = db.bytes;
+  s->hdr = db.hdr;
+  s->d_blob = db.d_blob;
+  db.d_blob = nullptr;
+  st = adopt_blob(s);
+  if (st != RT_OK) { rt_scene_destroy(s); return st; }
+  *out = s;
+  return RT_OK;
+}
+
 int rt_scene_create(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects,
                     int num_objects, rt_scene **out) {
   // RT_B200_TOPOLOGY=reference: A/B switch for callers that cannot pass flags (the drop-in launcher)
@@ -590,6 +610,29 @@ int rt_scene_create_ex(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, con
   // the traversal tree is built on this GPU (rt_sah_gpu.cu) unless RT_SCENE_HOST_SAH / RT_B200_SAH=host asks for the host twin
   set_sah_device_builder(&build_sah_device);
   if (const char *e = std::getenv("RT_B200_SAH")) if (std::strcmp(e, "host") == 0) scene_flags |= RT_SCENE_HOST_SAH;
+  bool host_flatten = (scene_flags & (RT_SCENE_HOST_FLATTEN | RT_SCENE_HOST_SAH | RT_SCENE_REFERENCE_TOPOLOGY)) != 0;
+  if (const char *e = std::getenv("RT_B200_FLATTEN")) if (std::strcmp(e, "host") == 0) host_flatten = true;
+  if (!host_flatten) {
+    // the flattener on the GPU (rt_flatten_gpu.cu); whatever it declines or fails at goes to the host twin below
+    DeviceBlob db;
+    std::string derr;
+    st = flatten_scene_device(data, bvh, objects, num_objects, scene_flags, db, derr);
+    if (st == RT_OK) {
+      const double flat_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+      const FlattenStats fs = last_flatten_stats();
+      st = scene_from_device_blob(db, out);
+      if (st == RT_OK) {
+        (*out)->info.flatten_ms = flat_ms;
+        (*out)->info.sah_builder = fs.sah_builder;
+        (*out)->info.sah_build_ms = fs.sah_ms;
+        (*out)->info.sah_device_ms = fs.sah_device_ms;
+        (*out)->info.flattener = 1;
+        return RT_OK;
+      }
+    }
+    if (std::getenv("RT_FLATTEN_TIMING")) std::fprintf(stderr, "[flatten gpu] declined (%d %s): host flattener\n", st, derr.c_str());
+    cudaGetLastError();
+  }
   st = flatten_scene(data, bvh, objects, num_objects, scene_flags, blob, err);
   if (st != RT_OK) { set_error(err); return st; }
   const double flat_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

@@ -24,6 +24,7 @@ static SahDeviceFn g_sah_device = nullptr;
 static thread_local FlattenStats g_stats;
 void set_sah_device_builder(SahDeviceFn fn) { g_sah_device = fn; }
 const FlattenStats &last_flatten_stats() { return g_stats; }
+FlattenStats &mutable_flatten_stats() { return g_stats; }
 namespace {
 
 // Contiguous ranges of [0, n) on the host threads (the flattener's per-triangle passes and section copies are

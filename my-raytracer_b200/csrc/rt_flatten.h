@@ -21,8 +21,23 @@ struct FlattenStats {
   int sah_builder = 0;      // 0: no SAH tree built, 1: host builder, 2: device builder
   double sah_ms = 0.0;      // wall time of the tree build (device: including its transfers)
   double sah_device_ms = 0.0;
+  int flattener = 0;        // 0: host flattener (this file's twin rt_flatten.cpp), 1: device flattener (rt_flatten_gpu.cu)
 };
-const FlattenStats &last_flatten_stats();   // of the calling thread's last flatten_scene
+const FlattenStats &last_flatten_stats();   // of the calling thread's last flatten_scene / flatten_scene_device
+FlattenStats &mutable_flatten_stats();
+
+// The flattener on the GPU (rt_flatten_gpu.cu; CUDA library only): same inputs, the blob is built in HBM and handed over
+// as a device allocation (cudaMalloc; the caller owns it).  Returns RT_OK, or kFlattenUseHost when the scene is one the
+// device path leaves to flatten_scene (reference topology, root leaf, any malformed input: the host twin words the error),
+// or an rt_status of a CUDA failure (the caller may still fall back to the host twin).
+struct DeviceBlob {
+  unsigned char *d_blob = nullptr;
+  size_t bytes = 0;
+  BlobHeader hdr;
+};
+constexpr int kFlattenUseHost = -1;
+int flatten_scene_device(const rt_data_soa *data, const rt_bvh_nodes_soa *bvh, const rt_object *objects, int num_objects,
+                         unsigned flags, DeviceBlob &out, std::string &err);
 
 // Validates a blob received from another rank (magic, version, section bounds).
 int check_blob(const unsigned char *blob, size_t bytes, std::string &err);

@@ -276,3 +276,75 @@ def test_gpu_sah_builder_against_the_host_builder(rt, lib, gpu, name, kw):
             c = dev.render(*args, host.params(flags=fl))
             for k in ("hit_id", "hit_t", "rgba8", "pixels"):
                 assert np.array_equal(a[k], c[k]), (fl, k)
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("office", dict(width=480, height=270)),
+    ("rings", dict(width=210, height=150)),                    # PHONG vertex normals
+    ("textured", dict(width=256, height=144, tex_size=256)),   # uv records + texels
+    ("scatter", dict(width=256, height=144, n_objects=300)),   # triangle trees + a tree over analytic spheres
+    ("mixed_small", dict(width=160, height=120)),              # meshes, texture, spheres and a plane tested linearly
+])
+def test_device_flattener_against_the_host_flattener(rt, lib, gpu, name, kw):
+    """The blob emitted on the GPU (rt_flatten_gpu.cu, default) against the host flattener (RT_SCENE_HOST_FLATTEN) on the
+    same GPU-built tree: per-triangle sections byte-identical, the same tree structure under a different record numbering
+    (level order instead of DFS pre-order: equal record counts and equal traversal counters), the same frame bit for bit
+    on every kernel variant, and a reproducible blob."""
+    from my_raytracer_b200 import blobfmt
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    dev = rt.DeviceScene(host)
+    ref = rt.DeviceScene(host, scene_flags=gpu.RT_SCENE_HOST_FLATTEN)
+    assert dev.info()["flattener"] == 1 and ref.info()["flattener"] == 0
+    assert dev.info()["sah_builder"] == 2 and ref.info()["sah_builder"] == 2
+    ba, bb = dev.export_blob(), ref.export_blob()
+    ha, hb = blobfmt.header(ba), blobfmt.header(bb)
+    for k, v in hb.items():
+        assert ha[k] == v, (k, ha[k], v)               # every count, offset and extent of the header
+    n = ha["num_tris"]
+    for off, size in (("off_filter", 48 * n), ("off_exact", 80 * n), ("off_shade", 128 * n), ("off_tri_id", 4 * n),
+                      ("off_tri_pos", 4 * n), ("off_meshes", 128 * ha["num_meshes"]), ("off_objects", 176 * ha["num_objects"]),
+                      ("off_objfilt", 32 * ha["num_objects"]), ("off_texels", 16 * ha["num_texels"]),
+                      ("off_obj_order", 4 * ha["num_obj_tree"]), ("off_lin_idx", 4 * ha["num_lin"])):
+        o = ha[off]
+        assert ba[o:o + size] == bb[o:o + size], off
+    args = (host.camera, host.lights_pos, host.lights_color)
+    a = dev.render(*args, host.params(flags=gpu.RT_FLAG_COUNTERS))
+    b = ref.render(*args, host.params(flags=gpu.RT_FLAG_COUNTERS))
+    for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+        assert np.array_equal(a[k], b[k]), k
+    assert a["counters"] == b["counters"]              # the same tree walked in the same order
+    for fl in (gpu.RT_FLAG_NODES8, gpu.RT_FLAG_BINARY_NODES, gpu.RT_FLAG_EXACT_ONLY, gpu.RT_FLAG_WAVEFRONT):
+        c = dev.render(*args, host.params(flags=fl))
+        for k in ("hit_id", "hit_t", "rgba8", "pixels"):
+            assert np.array_equal(a[k], c[k]), (fl, k)
+    assert rt.DeviceScene(host).export_blob() == ba
+
+
+def test_device_flattener_leaves_malformed_scenes_to_the_host_flattener(rt, lib, gpu):
+    """Whatever the device flattener's validation rejects is flattened again by the host twin, which words the error:
+    same status and message as with RT_SCENE_HOST_FLATTEN."""
+    def attempt(mutate, flags):
+        host = rt.HostScene(rt.scenes.office(width=64, height=36), lib)
+        keep = mutate(host)
+        h = C.c_void_p()
+        st = lib.rt_scene_create_ex(C.byref(host.data), C.byref(host.bvh), host.objects, host.num_objects, flags, C.byref(h))
+        msg = lib.rt_last_error()
+        if st == 0:
+            lib.rt_scene_destroy(h)
+        del keep
+        return st, msg
+
+    def bad_child(host):
+        host.bvh.leftChildIdx_[0] = 2 * host.num_triangles + 5
+    def bad_vertex(host):
+        host.data.vertexIdx_[7] = host.data.tVertexCount_
+    def shared_leaf(host):
+        # the right child of the root becomes a copy of the left one: its triangles are referenced twice, others never
+        l = host.bvh.leftChildIdx_[0]
+        host.bvh.leftChildIdx_[l + 1] = host.bvh.leftChildIdx_[l]
+        host.bvh.triCount_[l + 1] = host.bvh.triCount_[l]
+        host.bvh.firstTriIdx_[l + 1] = host.bvh.firstTriIdx_[l]
+    for mutate in (bad_child, bad_vertex, shared_leaf):
+        st_d, msg_d = attempt(mutate, 0)
+        st_h, msg_h = attempt(mutate, gpu.RT_SCENE_HOST_FLATTEN)
+        assert st_d == st_h == gpu.RT_ERR_BAD_SCENE and msg_d == msg_h, (mutate.__name__, st_d, st_h, msg_d, msg_h)

@@ -18,7 +18,7 @@ def test_cabi_exports_every_declared_symbol(rt, lib):
     assert declared == set(capi.PROTOTYPES), declared ^ set(capi.PROTOTYPES)
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.rt_abi_version() == 5
+    assert lib.rt_abi_version() == 6
 
 
 def test_struct_layouts_match_reference_headers(rt):

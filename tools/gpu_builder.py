@@ -1,5 +1,7 @@
-"""Timing of the scene preparation: traversal tree on the GPU (default) vs on the host threads (RT_SCENE_HOST_SAH), flatten
-and upload, and the render time on either tree.  python tools/gpu_builder.py [--big N_OBJECTS]"""
+"""Timing of the scene preparation: records and traversal tree on the GPU (default), records on the host threads with the
+GPU-built tree (RT_SCENE_HOST_FLATTEN), everything on the host threads (RT_SCENE_HOST_SAH); flatten and upload, the render
+time on each blob and a checksum of the frame.  python tools/gpu_builder.py [--big N_OBJECTS]"""
+import hashlib
 import json
 import os
 import sys
@@ -23,7 +25,7 @@ out = {}
 for name, desc, spp, gpu_build in jobs:
     host = rt.HostScene(desc, lib, gpu_build=gpu_build)
     res = {}
-    for label, fl in (("device", 0), ("host", capi.RT_SCENE_HOST_SAH), ("device_again", 0)):
+    for label, fl in (("device", 0), ("host_flatten", capi.RT_SCENE_HOST_FLATTEN), ("host", capi.RT_SCENE_HOST_SAH), ("device_again", 0)):
         t = time.perf_counter()
         dev = rt.DeviceScene(host, scene_flags=fl)
         wall = (time.perf_counter() - t) * 1e3
@@ -33,6 +35,7 @@ for name, desc, spp, gpu_build in jobs:
             r = dev.render(host.camera, host.lights_pos, host.lights_color, host.params(spp_grid=spp), want=("rgba8",))
             ms.append(dev.last_kernel_ms())
         res[label] = {"create_wall_ms": wall, "flatten_ms": info["flatten_ms"], "upload_ms": info["upload_ms"],
+                      "flattener": info["flattener"], "frame_sha1": hashlib.sha1(r["rgba8"].tobytes()).hexdigest()[:12],
                       "sah_builder": info["sah_builder"], "sah_build_ms": info["sah_build_ms"], "sah_device_ms": info["sah_device_ms"],
                       "kernel_ms": min(ms[1:]), "nodes": info["num_nodes_traversal"], "wide": info["num_nodes_wide"],
                       "wide8": info["num_nodes_wide8"], "depth": info["max_depth_bvh"]}
