@@ -56,7 +56,7 @@ WORKLOADS = {
 ALIASES = {"office": "office_34k_1920x1080_1spp", "bigscene": "bigscene_10m_4k_4spp"}
 # committed `ncu --set full` summaries the roofline's DRAM traffic is read from (newest first)
 NCU_SUMMARIES = {
-    "office_34k_1920x1080_1spp": ["profiles/r02_ncu_render_kernel_office.md", "profiles/r01_ncu_render_kernel_v8.md"],
+    "office_34k_1920x1080_1spp": ["profiles/r02_ncu_render_kernel_office_final.md", "profiles/r02_ncu_render_kernel_office.md", "profiles/r01_ncu_render_kernel_v8.md"],
     "bigscene_10m_4k_4spp": ["profiles/r02_ncu_render_kernel_10M.md", "profiles/r01_ncu_render_kernel_v7_10M.md"],
 }
 
