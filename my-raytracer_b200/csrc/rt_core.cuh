@@ -26,6 +26,19 @@
 #ifndef RT_CACHE_LDIR
 #define RT_CACHE_LDIR 1
 #endif
+// Experiment ("full-lane leaf tests"): a hit leaf range of the 4-wide step is not intersected at once
+// but kept in two registers; the warp intersects the postponed leaves together once RT_LEAF_DEFER_MIN lanes hold one (or
+// nobody is left to wait for).  RT_LEAF_DEFER_SPEC 1: a lane holding a leaf keeps walking (speculatively, with its stale
+// distance bound); 0: it waits.  Results are identical (every candidate still gets the exact test).  0 = off (default).
+#ifndef RT_LEAF_DEFER
+#define RT_LEAF_DEFER 0
+#endif
+#ifndef RT_LEAF_DEFER_MIN
+#define RT_LEAF_DEFER_MIN 16
+#endif
+#ifndef RT_LEAF_DEFER_SPEC
+#define RT_LEAF_DEFER_SPEC 1
+#endif
 
 namespace rtb {
 
@@ -76,6 +89,9 @@ struct Hot {
   int sp;
   int mode;
   int found;   // any-hit result
+#if RT_LEAF_DEFER
+  int lf_first, lf_last; // postponed leaf range of the 4-wide step (lf_last > lf_first: one is held)
+#endif
   int special; // rare-path flags, tested with ONE predicate in the hot loop:
                //   S_XPAR: direction.x == 0 exactly, the reference's 0/0 slab quirk applies (rt_types.h NodeMaxX)
                //   S_OBJ : the ray is walking the tree over the analytic spheres (before the triangle tree)
@@ -227,6 +243,9 @@ RT_HD void start_ray(const Ctx &c, Hot &H, const Cold<S> &C, const D3 &origin, c
   H.best_id = -1;
   H.found = 0;
   H.sp = 0;
+#if RT_LEAF_DEFER
+  H.lf_first = H.lf_last = 0;
+#endif
   double best = tmax;
   float othi = thi_of(best);
   const bool exact_only = (c.fp.flags & 1) != 0;
@@ -475,8 +494,27 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   unsigned lm = (h0 && n0 > 0 ? 1u : 0u) | (h1 && n1 > 0 ? 2u : 0u) | (h2 && n2 > 0 ? 4u : 0u) | (h3 && n3 > 0 ? 8u : 0u);
   if (lm) {
     h0 = h0 && !(lm & 1u); h1 = h1 && !(lm & 2u); h2 = h2 && !(lm & 4u); h3 = h3 && !(lm & 8u);
+#if RT_LEAF_DEFER
+    // neighbouring leaf children own adjacent ranges: a run of hit leaves is ONE range
+    const unsigned low = lm & (0u - lm);
+    const bool one_run = ((lm + low) & lm) == 0u;
+    if (H.lf_last > H.lf_first) {               // already holding one: intersect it now (this lane only)
+      leaf_test<COUNT, false>(c, H, C, H.lf_first, H.lf_last);
+      H.lf_first = H.lf_last = 0;
+      if (H.found) { H.node = -1; return; }
+    }
+    if (one_run) {
+      const int kf = first_bit(lm), kl = (lm & 8u) ? 3 : ((lm & 4u) ? 2 : ((lm & 2u) ? 1 : 0));
+      H.lf_first = kf == 0 ? r0 : (kf == 1 ? r1 : (kf == 2 ? r2 : r3));
+      H.lf_last = (kl == 0 ? r0 + n0 : (kl == 1 ? r1 + n1 : (kl == 2 ? r2 + n2 : r3 + n3)));
+    } else {
+      wide_leaves<COUNT>(c, H, C, lm, r0, r1, r2, r3, n0, n1, n2, n3);
+      if (H.found) return;
+    }
+#else
     wide_leaves<COUNT>(c, H, C, lm, r0, r1, r2, r3, n0, n1, n2, n3);
     if (H.found) return;
+#endif
     // a nearer hit may have been found: surviving interior children are re-checked when visited / popped
   }
   int node, sp = H.sp;
@@ -502,6 +540,17 @@ RT_HD void trav_step4(const Ctx &c, Hot &H, const Cold<S> &C, StackEntry *stk) {
   H.node = node;
   H.sp = sp;
 }
+
+#if RT_LEAF_DEFER
+// Intersect the lane's postponed leaf (called warp-wide by the kernel loop when enough lanes hold one).
+template <int COUNT, int S> RT_HD void flush_leaf(const Ctx &c, Hot &H, const Cold<S> &C) {
+  if (H.lf_last > H.lf_first) {
+    leaf_test<COUNT, false>(c, H, C, H.lf_first, H.lf_last);
+    H.lf_first = H.lf_last = 0;
+    if (H.found) H.node = -1;
+  }
+}
+#endif
 
 // One step through the 8-wide tree (K_WIDE8 kernels, ordinary rays, triangle tree only): one 256-byte Node8Rec (eight
 // 32-byte loads), eight independent conservative slab tests (48 FFMA2), hit leaf children intersected at once, the

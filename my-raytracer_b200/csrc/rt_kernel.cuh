@@ -90,6 +90,9 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
   H.found = 0;
   H.best_id = -1;
   H.special = 0;
+#if RT_LEAF_DEFER
+  H.lf_first = H.lf_last = 0;
+#endif
   const long long slots = work_slots(c);
   const long long nchunks = a.dyn_counter ? pool_chunks(c) : 0;
   const unsigned lane = threadIdx.x & 31u;
@@ -177,9 +180,27 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
         }
       } else if (COUNT & K_WIDE) {
         // ordinary rays walk the 4-wide tree: half the dependent steps, four independent box tests in each
+#if RT_LEAF_DEFER
+        for (;;) {
+          const unsigned pend = __ballot_sync(kFullMask, H.lf_last > H.lf_first);
+          const unsigned walking = __ballot_sync(kFullMask, H.node >= 0);
+          if (!(pend | walking)) break;
+          // intersect the postponed leaves together: enough lanes hold one, or nobody without one is still walking
+          if (pend && (__popc(pend) >= RT_LEAF_DEFER_MIN || (walking & ~pend) == 0u)) {
+            flush_leaf<COUNT>(c, H, C);
+            continue;
+          }
+#if RT_LEAF_DEFER_SPEC
+          if (H.node >= 0) trav_step4<COUNT>(c, H, C, stk);
+#else
+          if (H.node >= 0 && !(H.lf_last > H.lf_first)) trav_step4<COUNT>(c, H, C, stk);
+#endif
+        }
+#else
         while (__any_sync(kFullMask, H.node >= 0)) {
           if (H.node >= 0) trav_step4<COUNT>(c, H, C, stk);
         }
+#endif
       } else {
         while (__any_sync(kFullMask, H.node >= 0)) {
           if (H.node >= 0) trav_step<COUNT, false>(c, H, C, stk);

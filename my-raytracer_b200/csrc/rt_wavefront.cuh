@@ -241,6 +241,9 @@ __global__ void __launch_bounds__(kBlockThreads, RT_WF_MIN_BLOCKS) wf_trace_kern
     const long long p = (b0 + j) * 32 + lane;
     Hot H;
     H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0;
+#if RT_LEAF_DEFER
+    H.lf_first = H.lf_last = 0;
+#endif
     const bool has = p < a.w.npaths && wf_ray_start<COUNT>(c, a.w, p, kind, a.sample, H, T);
     if (!__any_sync(kFullMask, has)) continue;
     // the traversal loops of rt_kernel.cuh, verbatim: warp-uniform step loop, d.x == 0 rays parked for the second loop
@@ -248,6 +251,9 @@ __global__ void __launch_bounds__(kBlockThreads, RT_WF_MIN_BLOCKS) wf_trace_kern
       if (COUNT & K_WIDE) {
         while (__any_sync(kFullMask, H.node >= 0)) {
           if (H.node >= 0) trav_step4<COUNT>(c, H, T, stk);
+#if RT_LEAF_DEFER
+          flush_leaf<COUNT>(c, H, T);     // (experiment builds: the wavefront does not postpone leaves)
+#endif
         }
       } else {
         while (__any_sync(kFullMask, H.node >= 0)) {
