@@ -142,6 +142,10 @@ typedef struct rt_render_params {
 #define RT_FLAG_NODES8      64 /* A/B: ordinary rays walk the 8-wide twin of the triangle tree (256-byte records, eight slab
                                   tests per step) instead of the 4-wide one; scenes without one (a tree over analytic
                                   spheres, tiny meshes) ignore the flag.  RT_B200_NODES=8 selects it for every frame. */
+#define RT_FLAG_SEQUENTIAL_SAMPLES 128 /* A/B: with a 2x2 or 4x4 sub-pixel grid every lane traces all samples of its pixel one
+                                  after the other (the round-1 schedule) instead of one sample per lane (a warp = 8 or 2 pixels,
+                                  the samples of a pixel summed in sample order: bit-identical pixels, 4 / 16 x finer work
+                                  units, closer rays per warp) */
 #define RT_FLAG_MEGAKERNEL  32 /* always the one persistent kernel (overrides RT_B200_PIPELINE) */
 
 /* Output buffers; any pointer may be NULL.  All are W*H entries, index y*W + x

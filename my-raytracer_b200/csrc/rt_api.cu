@@ -378,6 +378,19 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
     gp = gp < lim ? gp : lim;
   }
   const bool obj = s->hdr.obj_root >= 0; // tree over analytic spheres: the kernel variant that can walk it
+  // 2x2 / 4x4 sub-pixel grids: one sample per lane (K_SPL kernels, rt_kernel.cuh) unless the scene refills single lanes
+  // (>= 32 analytic primitives), the frame is instrumented or walks the 8-wide records (A/B paths keep the sequential loop)
+  const int s2 = fp.spp_grid * fp.spp_grid;
+  const bool spl = RT_SAMPLE_LANES && !(fp.flags & RT_FLAG_SEQUENTIAL_SAMPLES) && (s2 == 4 || s2 == 16) && !count && !wide8 &&
+                   s->hdr.num_objects < kPartialRefillObjects;
+  if (spl) {
+    switch ((obj ? K_OBJ : 0) | (wide ? K_WIDE : 0)) {
+      case 0: render_kernel<K_SPL><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+      case K_OBJ: render_kernel<K_SPL | K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+      case K_WIDE: render_kernel<K_SPL | K_WIDE><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+      default: render_kernel<K_SPL | K_WIDE | K_OBJ><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
+    }
+  } else
   switch ((count ? K_COUNT : 0) | (obj ? K_OBJ : 0) | (wide ? K_WIDE : 0) | (wide8 ? K_WIDE8 : 0)) {
     case K_WIDE | K_WIDE8: render_kernel<K_WIDE | K_WIDE8><<<gp, kBlockThreads, s->extra_smem, st>>>(a); break;
     case K_WIDE | K_WIDE8 | K_COUNT: render_kernel<K_WIDE | K_WIDE8 | K_COUNT><<<gc, kBlockThreads, s->extra_smem, st>>>(a); break;

@@ -103,7 +103,9 @@ enum Special : int { S_XPAR = 1, S_OBJ = 2 };
 // K_WIDE = ordinary rays walk the 4-wide twins of the traversal trees (Node4Rec, trav_step4): the triangle tree's
 // and, with K_OBJ, the object tree's (the host picks K_WIDE only when every tree the scene has owns a twin).
 // K_WIDE8 = ordinary rays walk the 8-wide twin of the triangle tree (Node8Rec, trav_step8); never together with K_OBJ.
-enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2, K_WIDE = 4, K_WIDE8 = 8 };
+// K_SPL = the sub-pixel samples of a pixel are traced by neighbouring LANES (rt_kernel.cuh) instead of one after the other by
+// one lane; launched for 2x2 and 4x4 sample grids.
+enum KernelCfg : int { K_COUNT = 1, K_OBJ = 2, K_WIDE = 4, K_WIDE8 = 8, K_SPL = 16 };
 
 struct Mat {
   D3 ka, ks;
@@ -704,6 +706,11 @@ template <int S> RT_HD void write_pixel(const Ctx &c, const Cold<S> &C) {
 }
 
 template <int COUNT, int S> RT_HD void sample_done(const Ctx &c, Hot &H, const Cold<S> &C) {
+  if (COUNT & K_SPL) {   // the sample stays in CD_COL until the warp sums the samples of each pixel (rt_kernel.cuh)
+    H.mode = M_IDLE;
+    H.node = -1;
+    return;
+  }
   C.set(CD_ACC, add(C.v(CD_ACC), C.v(CD_COL)));
   const int sample = C.i(CI_SAMPLE) + 1;
   C.i(CI_SAMPLE) = sample;
@@ -877,6 +884,14 @@ template <int COUNT, int S> RT_HD void begin_pixel(const Ctx &c, Hot &H, const C
   C.i(CI_PY) = py;
   C.i(CI_SAMPLE) = 0;
   C.set(CD_ACC, mk(0.0, 0.0, 0.0));
+  start_primary<COUNT>(c, H, C);
+}
+
+// Begin ONE sub-pixel sample of a pixel (sample-per-lane mode of render_kernel).
+template <int COUNT, int S> RT_HD void begin_sample(const Ctx &c, Hot &H, const Cold<S> &C, int px, int py, int sample) {
+  C.i(CI_PX) = px;
+  C.i(CI_PY) = py;
+  C.i(CI_SAMPLE) = sample;
   start_primary<COUNT>(c, H, C);
 }
 

@@ -44,6 +44,9 @@ struct KernelArgs {
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 4
 #endif
+#ifndef RT_SAMPLE_LANES
+#define RT_SAMPLE_LANES 1   // 0: A/B, every lane traces all sub-pixel samples of its pixel one after the other (rt_api.cu)
+#endif
 template <int COUNT>
 __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(const __grid_constant__ KernelArgs a) {
   unsigned int cnt[(COUNT & K_COUNT) ? C_COUNT : 1];
@@ -93,10 +96,20 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
 #if RT_LEAF_DEFER
   H.lf_first = H.lf_last = 0;
 #endif
-  const long long slots = work_slots(c);
-  const long long nchunks = a.dyn_counter ? pool_chunks(c) : 0;
   const unsigned lane = threadIdx.x & 31u;
   const bool partial_refill = c.sv.num_objects >= kPartialRefillObjects;
+  // Sub-pixel samples: with a 2x2 or 4x4 grid the s^2 samples of a pixel go to s^2 neighbouring LANES (a warp = 8 or 2
+  // pixels) instead of being traced one after the other by one lane.  A work slot is then (pixel, sample): the unit of
+  // work a warp fetches costs 1/s^2 of a tile with all its samples, so the tail of a frame (or of a GPU's share of it)
+  // is that much shorter, and the rays of a warp are closer together.  The samples of a pixel are summed in sample order
+  // when the whole warp has finished (same additions as the sequential loop: bit-identical pixels).
+  const int s2 = c.fp.spp_grid * c.fp.spp_grid;
+  // (K_SPL kernels only: the host launches them for s^2 = 4 or 16 when lanes are refilled a warp at a time.)
+  const bool sample_lanes = (COUNT & K_SPL) != 0;
+  const int spl = sample_lanes ? s2 : 1;     // lanes per pixel
+  bool had = false;                          // this lane holds a finished sample that is not summed yet
+  const long long slots = work_slots(c) * spl;
+  const long long nchunks = a.dyn_counter ? pool_chunks(c) : 0;
   bool exhausted = false;   // warp-uniform: no work left anywhere
   bool local_done = false;  // warp-uniform: this rank's static share is drained
   long long wp_next = 0, wp_end = 0; // warp-private range of dynamic-pool slots (warp-uniform)
@@ -114,6 +127,25 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
     // Exception: scenes dominated by the linear list of analytic primitives (the reference has no BVH over
     // objects_): every ray walks the same list in lockstep whatever its generation, so there is no coherence
     // to protect and full lanes win (molecule, 602 objects: 2.9 ms against 4.1 ms).
+    if (sample_lanes && idle == kFullMask && __any_sync(kFullMask, had)) {
+      // every lane of the warp has finished its sample: ACC = ((0 + c0) + c1) + ... in sample order, first lane writes
+      const int g0 = (int)lane & ~(spl - 1);
+      D3 col = mk(0.0, 0.0, 0.0);
+      if (had) col = C.v(CD_COL);
+      D3 acc = mk(0.0, 0.0, 0.0);
+      for (int k = 0; k < spl; ++k) {
+        D3 ck;
+        ck.x = __shfl_sync(kFullMask, col.x, g0 + k);
+        ck.y = __shfl_sync(kFullMask, col.y, g0 + k);
+        ck.z = __shfl_sync(kFullMask, col.z, g0 + k);
+        acc = add(acc, ck);
+      }
+      if (had && (int)lane == g0) {
+        C.set(CD_ACC, acc);
+        write_pixel(c, C);
+      }
+      had = false;
+    }
 #ifdef RT_REFILL_PARTIAL
     if (idle != 0u && !exhausted) {
 #else
@@ -133,7 +165,9 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
         } else if (H.mode == M_IDLE) {
           const long long mine = (long long)base + rank_in_idle;
           int px, py;
-          if (mine < slots && work_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
+          if (sample_lanes) {
+            if (mine < slots && work_to_pixel(c, mine / spl, px, py)) { begin_sample<COUNT>(c, H, C, px, py, (int)(mine % spl)); had = true; }
+          } else if (mine < slots && work_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
         }
       } else {
         // cross-GPU dynamic tail: the warp claims dyn_chunk tiles at a time with ONE system-scope atomic
@@ -150,15 +184,17 @@ __global__ void __launch_bounds__(kBlockThreads, RT_MIN_BLOCKS) render_kernel(co
           if (q >= (unsigned long long)nchunks) {
             exhausted = true;
           } else {
-            wp_next = (long long)q * c.fp.dyn_chunk * (kTileW * kTileH);
-            wp_end = wp_next + (long long)c.fp.dyn_chunk * (kTileW * kTileH);
+            wp_next = (long long)q * c.fp.dyn_chunk * (kTileW * kTileH) * spl;
+            wp_end = wp_next + (long long)c.fp.dyn_chunk * (kTileW * kTileH) * spl;
           }
         }
         if (!exhausted) {
           const long long mine = wp_next + rank_in_idle;
           wp_next += n;
           int px, py;
-          if (H.mode == M_IDLE && mine < wp_end && pool_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
+          if (sample_lanes) {
+            if (mine < wp_end && pool_to_pixel(c, mine / spl, px, py)) { begin_sample<COUNT>(c, H, C, px, py, (int)(mine % spl)); had = true; }
+          } else if (H.mode == M_IDLE && mine < wp_end && pool_to_pixel(c, mine, px, py)) begin_pixel<COUNT>(c, H, C, px, py);
         }
       }
     }

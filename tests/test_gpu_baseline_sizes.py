@@ -348,3 +348,39 @@ def test_device_flattener_leaves_malformed_scenes_to_the_host_flattener(rt, lib,
         st_d, msg_d = attempt(mutate, 0)
         st_h, msg_h = attempt(mutate, gpu.RT_SCENE_HOST_FLATTEN)
         assert st_d == st_h == gpu.RT_ERR_BAD_SCENE and msg_d == msg_h, (mutate.__name__, st_d, st_h, msg_d, msg_h)
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("office", dict(width=322, height=181)),
+    ("textured", dict(width=200, height=120, tex_size=128)),
+    ("scatter", dict(width=160, height=100, n_objects=20)),    # triangle trees + a tree over analytic spheres (K_OBJ kernels)
+    ("mixed_small", dict(width=161, height=99)),               # ragged last tile column / row
+])
+def test_one_sample_per_lane_equals_the_sequential_sample_loop(rt, lib, gpu, name, kw):
+    """2x2 and 4x4 sub-pixel grids: the samples of a pixel traced by neighbouring lanes and summed in sample order
+    (default, K_SPL kernels) give the same FP64 pixels, bit for bit, as one lane tracing them one after the other
+    (RT_FLAG_SEQUENTIAL_SAMPLES) — on the whole frame, on a rank's tile share with the dynamic tile queue, and on the
+    4-wide and the binary records.  A 3x3 grid (9 lanes do not divide a warp) keeps the sequential loop."""
+    import torch
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    dev = rt.DeviceScene(host)
+    args = (host.camera, host.lights_pos, host.lights_color)
+    for spp in (2, 4, 3):
+        a = dev.render(*args, host.params(spp_grid=spp), want=("rgba8", "pixels"))
+        b = dev.render(*args, host.params(spp_grid=spp, flags=gpu.RT_FLAG_SEQUENTIAL_SAMPLES), want=("rgba8", "pixels"))
+        assert np.array_equal(a["pixels"], b["pixels"]) and np.array_equal(a["rgba8"], b["rgba8"]), spp
+        assert a["pixels"][..., :3].max() > 0.0
+        c = dev.render(*args, host.params(spp_grid=spp, flags=gpu.RT_FLAG_BINARY_NODES), want=("pixels",))
+        assert np.array_equal(a["pixels"], c["pixels"]), spp
+    # two ranks' shares of one frame, the last tiles from the dynamic queue (one counter, as on one GPU in the tests)
+    counter = torch.zeros(1, dtype=torch.int64, device="cuda")
+    W, H = host.camera.width, host.camera.height
+    tiles = ((W + 7) // 8) * ((H + 3) // 4)
+    whole = dev.render(*args, host.params(spp_grid=2), want=("pixels",))["pixels"]
+    acc = np.zeros_like(whole)
+    for rank in (0, 1):
+        p = host.params(spp_grid=2, tile=(rank, 2, 4), dyn=(tiles // 3, 2, counter.data_ptr()))
+        part = dev.render(*args, p, want=("pixels",))["pixels"]
+        acc = np.where(part != 0.0, part, acc)
+    torch.cuda.synchronize()
+    assert np.array_equal(acc, whole)
