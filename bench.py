@@ -316,6 +316,8 @@ def run_b200(args):
     depth = int(os.environ.get("RT_FRAMES_IN_FLIGHT", "4" if big else ("8" if world >= 2 else "4")))
     # the wavefront shards tiles statically only (no cross-GPU dynamic tail)
     dyn_fraction = float(os.environ.get("RT_DYN_FRACTION", ("0.3" if big else "0.15") if args.pipeline == "megakernel" else "0"))
+    # tiles per claim from the cross-GPU dynamic queue: a warp renders its claim tile by tile, so the claim is the tail's granularity
+    dyn_chunk = int(os.environ.get("RT_DYN_CHUNK", "8"))
     pflags = capi.RT_FLAG_WAVEFRONT if args.pipeline == "wavefront" else capi.RT_FLAG_MEGAKERNEL
     FLUSH = int(os.environ.get("RT_FLUSH_MB", "160")) * 1024 * 1024             # > 126 MB L2 (env: experiments only)
     # 0 = full-width grids (one GPU); half-width at 2-4 GPUs; quarter-width at 8
@@ -339,7 +341,7 @@ def run_b200(args):
     def make_pipe(mode):
         rot = mode == "rotate" and ncopies > 1
         return rdist.FramePipeline(lib, [c.handle for c in copies] if rot else scene.handle, host, dev, W, H, depth=depth,
-                                   ring=depth + 2, tile_chunk=chunk, dyn_fraction=dyn_fraction,
+                                   ring=depth + 2, tile_chunk=chunk, dyn_fraction=dyn_fraction, dyn_chunk=dyn_chunk,
                                    flush_bytes=FLUSH if mode in ("inline", "side") else 0, ctas_per_sm=ctas,
                                    flush_mode=mode if mode in ("inline", "side") else "off",
                                    spp_grid=spp_grid, shared_host=shared, flags=pflags)

@@ -78,14 +78,15 @@ def wrap_device_ptr(ptr: int, nbytes: int, device=None) -> torch.Tensor:
     return torch.as_tensor(_DevPtr(ptr, nbytes), device=dev)
 
 
-def dyn_split(width: int, height: int, world: int, fraction: float = 0.15):
+def dyn_split(width: int, height: int, world: int, fraction: float = 0.15, chunk: int = 8):
     """How many of the frame's 8x4 tiles go to the cross-GPU dynamic tail queue (the last ones in tile
-    order) and how many tiles one claim takes.  world == 1: none."""
+    order) and how many tiles one claim takes (a warp renders the tiles of its claim one after the other, so the claim
+    is also the granularity of the frame's tail: 8 for cheap tiles, fewer when a tile is expensive).  world == 1: none."""
     ntiles = ((width + 7) // 8) * ((height + 3) // 4)
     if world <= 1:
         return 0, 0
     dyn_tiles = int(ntiles * fraction)
-    return dyn_tiles, 8
+    return dyn_tiles, max(1, int(chunk))
 
 
 class SharedHostFrames:
@@ -176,7 +177,8 @@ class FramePipeline:
     """
 
     def __init__(self, lib, scene_handle, host_scene, device, width, height, depth=2, ring=4, tile_chunk=None,
-                 dyn_fraction=0.15, flush_bytes=0, ctas_per_sm=0, flush_mode="inline", spp_grid=1, shared_host=None, flags=0):
+                 dyn_fraction=0.15, flush_bytes=0, ctas_per_sm=0, flush_mode="inline", spp_grid=1, shared_host=None, flags=0,
+                 dyn_chunk=8):
         """flush_mode: "inline" = the L2-evicting fill runs on the frame's own stream ahead of its kernel; "side" = one
         fill per frame on a stream of its own, paced by the frames (frame f + depth waits for fill f) but not
         serialised ahead of the kernel; "off".  shared_host: SharedHostFrames for host_io at world > 1 (zero-copy
@@ -222,7 +224,7 @@ class FramePipeline:
         self.fb_ptr, self.ctr_ptr = fb.value, ctr.value
         self.fb_view = wrap_device_ptr(self.fb_ptr, nb * self.ring, device) if self.rank == 0 else None
         self.ctr_view = wrap_device_ptr(self.ctr_ptr, 64 * self.ring, device) if self.rank == 0 else None
-        self.dyn_tiles, self.dyn_chunk = dyn_split(width, height, self.world, dyn_fraction)
+        self.dyn_tiles, self.dyn_chunk = dyn_split(width, height, self.world, dyn_fraction, dyn_chunk)
         self.tile = tile_share(self.rank, self.world, tile_chunk) if self.world > 1 else (0, 1, 1)
         self.compute = [torch.cuda.Stream(device=device) for _ in range(self.depth)]
         self.comm = torch.cuda.Stream(device=device)
