@@ -146,6 +146,11 @@ typedef struct rt_render_params {
                                   after the other (the round-1 schedule) instead of one sample per lane (a warp = 8 or 2 pixels,
                                   the samples of a pixel summed in sample order: bit-identical pixels, 4 / 16 x finer work
                                   units, closer rays per warp) */
+#define RT_FLAG_RAY_PARALLEL 256 /* the rays of a path on neighbouring lanes (rp_render_kernel): after a hit its shadow rays (one
+                                  lane per light) and its mirror ray are traced together, a path advances one bounce per
+                                  round and a warp holds 8 paths instead of 32 pixels.  For frames that are chains of
+                                  dependent rays rather than throughput (<= 350 k pixels, deep mirror paths); bit-identical
+                                  pixels.  RT_B200_PIPELINE=rayparallel selects it for every frame it covers. */
 #define RT_FLAG_MEGAKERNEL  32 /* always the one persistent kernel (overrides RT_B200_PIPELINE) */
 
 /* Output buffers; any pointer may be NULL.  All are W*H entries, index y*W + x
@@ -329,7 +334,8 @@ int rt_get_counters(const rt_scene *scene, rt_counters *out);
 /* CUDA-event time of the last rt_render / rt_render_device kernel on this scene (ms);
  * synchronises on the end event. */
 int rt_last_kernel_ms(const rt_scene *scene, float *ms);
-/* Which pipeline the last frame of this scene ran on: 0 = the persistent kernel, 1 = the wavefront (RT_FLAG_WAVEFRONT
+/* Which pipeline the last frame of this scene ran on: 0 = the persistent kernel, 2 = the ray-parallel persistent kernel
+ * (RT_FLAG_RAY_PARALLEL), 1 = the wavefront (RT_FLAG_WAVEFRONT
  * asks for it; frames it does not cover fall back). */
 int rt_last_pipeline(const rt_scene *scene, int *pipeline);
 

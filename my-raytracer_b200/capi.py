@@ -16,7 +16,7 @@ RT_OK = 0
 RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_BAD_SCENE, RT_ERR_LIMIT, RT_ERR_OOM = 1, 2, 3, 4, 5, 6
 RT_SPHERE, RT_PLANE = 0, 1
 RT_FLAG_EXACT_ONLY, RT_FLAG_COUNTERS, RT_FLAG_NO_CLEAR, RT_FLAG_BINARY_NODES = 1, 2, 4, 8
-RT_FLAG_WAVEFRONT, RT_FLAG_MEGAKERNEL, RT_FLAG_NODES8, RT_FLAG_SEQUENTIAL_SAMPLES = 16, 32, 64, 128
+RT_FLAG_WAVEFRONT, RT_FLAG_MEGAKERNEL, RT_FLAG_NODES8, RT_FLAG_SEQUENTIAL_SAMPLES, RT_FLAG_RAY_PARALLEL = 16, 32, 64, 128, 256
 RT_SCENE_REFERENCE_TOPOLOGY = 1
 RT_SCENE_HOST_SAH = 2
 RT_SCENE_HOST_FLATTEN = 4

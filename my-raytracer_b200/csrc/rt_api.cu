@@ -73,6 +73,8 @@ struct rt_scene {
   } wf[kRing];
   int grid_wf[4] = {0, 0, 0, 0};         // resident CTAs x SMs of wf_trace_kernel<cfg>, cfg = (K_OBJ ? 1 : 0) | (K_WIDE ? 2 : 0)
   int wavefront_default = 0;             // RT_B200_PIPELINE=wavefront
+  int grid_rp[4] = {0, 0, 0, 0};         // the same for rp_render_kernel<cfg> (rays of a path on neighbouring lanes)
+  int rp_default = 0;                    // RT_B200_PIPELINE=rayparallel: every frame it covers; -1 (=persistent): never
   int last_pipeline = 0;                 // what the last launch ran: 0 persistent megakernel, 1 wavefront
   int grid_plain = 0, grid_count = 0;
   int grid_wide = 0, grid_wide_count = 0; // K_WIDE kernels (scenes whose trees all have 4-wide twins)
@@ -286,6 +288,15 @@ int adopt_blob(rt_scene *s) {
       s->grid_wf[k] = prop.multiProcessorCount * (occ > 0 ? occ : 1);
     }
     if (const char *e = std::getenv("RT_B200_PIPELINE")) s->wavefront_default = std::strcmp(e, "wavefront") == 0;
+    const void *kr[4] = {(const void *)rp_render_kernel<0>, (const void *)rp_render_kernel<K_OBJ>,
+                         (const void *)rp_render_kernel<K_WIDE>, (const void *)rp_render_kernel<K_WIDE | K_OBJ>};
+    for (int k = 0; k < 4; ++k) {
+      int occ = 0;
+      RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kr[k], kBlockThreads, 0));
+      s->grid_rp[k] = prop.multiProcessorCount * (occ > 0 ? occ : 1);
+    }
+    if (const char *e = std::getenv("RT_B200_PIPELINE"))
+      s->rp_default = std::strcmp(e, "rayparallel") == 0 ? 1 : (std::strcmp(e, "persistent") == 0 ? -1 : 0);
   }
   s->wide8_ok = s->wide_ok && wide8_usable(s->view);
   if (s->wide8_ok) {
@@ -326,6 +337,10 @@ int adopt_blob(rt_scene *s) {
   return RT_OK;
 }
 
+constexpr long long kRpAutoPixels = 400000;   // frames up to this many pixel samples default to the ray-parallel kernel
+#ifndef RT_RP_AUTO
+#define RT_RP_AUTO 0
+#endif
 bool wavefront_ok(const rt_scene *s, const FrameParams &fp, const int *d_list, const int *d_list_count);
 int launch_wavefront(rt_scene *s, const FrameParams &fp, const double *d_lpos, const double *d_lcol, const FrameOut &out,
                      cudaStream_t st);
@@ -376,6 +391,34 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
     const int lim = s->sm_count * s->ctas_per_sm;
     gc = gc < lim ? gc : lim;
     gp = gp < lim ? gp : lim;
+  }
+  // Small frames are chains of dependent rays, not throughput: the rays of a path on neighbouring lanes (rp_render_kernel,
+  // rt_wavefront.cuh).  Asked for by RT_FLAG_RAY_PARALLEL / RT_B200_PIPELINE=rayparallel, and by default for frames of at
+  // most kRpAutoPixels pixel samples; frames it does not cover (instrumented, pixel lists, dynamic tile queue, no light,
+  // more than 30) stay on the persistent kernel, as does everything under RT_FLAG_MEGAKERNEL.
+  {
+    const long long samples = (long long)fp.cam.width * fp.cam.height * fp.spp_grid * fp.spp_grid;
+    const bool covered = !count && !d_list && !d_list_count && fp.num_lights >= 1 && fp.num_lights <= kWfMaxLights &&
+                         fp.static_tiles == fp.tiles_x * fp.tiles_y && !(fp.flags & (RT_FLAG_MEGAKERNEL | RT_FLAG_NODES8));
+    const bool wanted = (fp.flags & RT_FLAG_RAY_PARALLEL) || s->rp_default > 0 ||
+                        (s->rp_default == 0 && RT_RP_AUTO && samples <= kRpAutoPixels);
+    if (covered && wanted) {
+      const bool objt = s->hdr.obj_root >= 0;
+      const int cfg = (objt ? 1 : 0) | (wide ? 2 : 0);
+      int grid = s->grid_rp[cfg];
+      if (s->ctas_per_sm > 0) { const int lim = s->sm_count * s->ctas_per_sm; grid = grid < lim ? grid : lim; }
+      switch (cfg) {
+        case 0: rp_render_kernel<0><<<grid, kBlockThreads, 0, st>>>(a); break;
+        case 1: rp_render_kernel<K_OBJ><<<grid, kBlockThreads, 0, st>>>(a); break;
+        case 2: rp_render_kernel<K_WIDE><<<grid, kBlockThreads, 0, st>>>(a); break;
+        default: rp_render_kernel<K_WIDE | K_OBJ><<<grid, kBlockThreads, 0, st>>>(a); break;
+      }
+      RT_CUDA(cudaGetLastError());
+      RT_CUDA(cudaEventRecord(s->ev1[slot], st));
+      s->timed = true;
+      s->last_pipeline = 2;
+      return RT_OK;
+    }
   }
   const bool obj = s->hdr.obj_root >= 0; // tree over analytic spheres: the kernel variant that can walk it
   // 2x2 / 4x4 sub-pixel grids: one sample per lane (K_SPL kernels, rt_kernel.cuh) unless the scene refills single lanes

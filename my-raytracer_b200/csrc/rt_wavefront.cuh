@@ -52,12 +52,14 @@ RT_HD Cold<0> wf_cold(const WfState &w, long long p) {
 
 // Start the ray of (path p, kind) if there is one.  kind: -1 primary ray of sub-pixel sample `sample`;
 // [0, L) shadow ray to that light; L the mirror ray.  T: the lane's scratch columns (CD_O, CD_D, CD_BEST_T).
+// work: the work slot the path renders (wavefront: the path index itself; ray-parallel kernel: the slot its warp fetched).
 template <int COUNT, int S>
-RT_HD bool wf_ray_start(const Ctx &c, const WfState &w, long long p, int kind, int sample, Hot &H, const Cold<S> &T) {
+RT_HD bool wf_ray_start(const Ctx &c, const WfState &w, long long p, int kind, int sample, Hot &H, const Cold<S> &T,
+                        long long work = -1) {
   const Cold<0> G = wf_cold(w, p);
   if (kind < 0) {
     int px, py;
-    if (!work_to_pixel(c, p, px, py)) { G.i(WI_FLAGS) = 0; return false; }
+    if (!work_to_pixel(c, work >= 0 ? work : p, px, py)) { G.i(WI_FLAGS) = 0; return false; }
     G.i(CI_PX) = px; G.i(CI_PY) = py; G.i(CI_SAMPLE) = sample;
     if (sample == 0) G.set(CD_ACC, mk(0.0, 0.0, 0.0));
     G.i(CI_DEPTH) = 0;
@@ -299,6 +301,102 @@ __global__ void __launch_bounds__(kBlockThreads) wf_shade_kernel(const __grid_co
 #pragma unroll
     for (int k = 0; k < C_COUNT; ++k)
       if (cnt[k]) atomicAdd(a.counters + k, (unsigned long long)cnt[k]);
+  }
+}
+
+// ---- the wavefront schedule INSIDE a persistent warp: rays of one path on neighbouring lanes --------------------------------
+// Small frames (BASELINE configs 1 and 3: <= 350 k pixels) do not fill the machine with work, they fill it with dependent
+// chains: a pixel of the rings scene is up to 6 hits x (2 shadow rays + 1 mirror ray), the persistent kernel traces them one
+// after the other on one lane, a warp's 32 chains advance in lockstep (every round costs the slowest lane's traversal), and
+// while the heaviest tiles run the other 2 000 warps have long finished (profiles/r02_rings_probe.log: one band of 440
+// tiles takes 0.58 ms ALONE on the whole GPU).  Here a path owns G = 2, 4 or 8 neighbouring lanes: after a hit, its shadow
+// rays (one lane per light) and its mirror ray are traced TOGETHER, so a path advances one bounce per round instead of
+// one ray per round, and a warp holds 32 / G paths, so there are G times more units of work to spread over the machine.
+// The stage functions are the wavefront's (wf_ray_start / wf_ray_finish / wf_shade: same arithmetic, same order of the
+// light sums, bit-identical pixels); the path state lives in shared memory instead of HBM and the group's first lane shades.
+#ifndef RT_RP_MIN_BLOCKS
+#define RT_RP_MIN_BLOCKS 4
+#endif
+constexpr int kRpMaxPathsPerWarp = 16;                            // G = 2
+constexpr int kRpPathsPerCta = kRpMaxPathsPerWarp * (kBlockThreads / 32);
+template <int COUNT>
+__global__ void __launch_bounds__(kBlockThreads, RT_RP_MIN_BLOCKS) rp_render_kernel(const __grid_constant__ KernelArgs a) {
+  unsigned int cnt[1];
+  Ctx c;
+  c.sv = a.sv; c.fp = a.fp;
+  c.light_pos = a.light_pos; c.light_col = a.light_col;
+  c.out = a.out;
+  c.pixel_list = a.pixel_list;
+  c.list_count = a.list_count_ptr ? *a.list_count_ptr : a.list_count;
+  c.cnt = cnt;
+  __shared__ double s_wd[WD_NUM * kRpPathsPerCta];
+  __shared__ int s_wi[WI_NUM * kRpPathsPerCta];
+  __shared__ unsigned char s_occl[kWfMaxLights * kRpPathsPerCta];
+  __shared__ double tcold[(CD_BEST_T + 1) * kBlockThreads];
+  WfState w;
+  w.wd = s_wd; w.wi = s_wi; w.occl = s_occl; w.npaths = kRpPathsPerCta;
+  Cold<kBlockThreads> T;
+  T.db = tcold + threadIdx.x;
+  T.ib = nullptr;
+  StackEntry stk[kStackMax];
+  const unsigned lane = threadIdx.x & 31u;
+  const int warp = (int)(threadIdx.x >> 5);
+  const int L = c.fp.num_lights;
+  const int G = L + 1 <= 2 ? 2 : (L + 1 <= 4 ? 4 : 8);           // lanes per path
+  const int per_warp = 32 / G;                                    // paths per warp
+  const int role = (int)lane & (G - 1);
+  const long long pcol = (long long)warp * kRpMaxPathsPerWarp + ((int)lane / G);   // the path's state column
+  const long long slots = work_slots(c);
+  const int s2 = c.fp.spp_grid * c.fp.spp_grid;
+  for (;;) {
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(a.work_counter, (unsigned long long)per_warp);
+    base = __shfl_sync(kFullMask, base, 0);
+    if ((long long)base >= slots) break;
+    const long long work = (long long)base + ((int)lane / G);
+    const bool mine = work < slots;
+    for (int sample = 0; sample < s2; ++sample) {
+      for (int b = 0;; ++b) {
+        const int nk = b == 0 ? 1 : L + 1;                        // ray kinds of this bounce: primary | L shadow rays + mirror
+        for (int k0 = 0; k0 < nk; k0 += G) {                      // (more kinds than lanes per path: several sub-rounds)
+          const int kind = b == 0 ? -1 : k0 + role;
+          Hot H;
+          H.mode = M_IDLE; H.node = -1; H.sp = 0; H.found = 0; H.best_id = -1; H.special = 0;
+#if RT_LEAF_DEFER
+          H.lf_first = H.lf_last = 0;
+#endif
+          const bool has = mine && (b == 0 ? role == 0 : kind < nk) && wf_ray_start<COUNT>(c, w, pcol, kind, sample, H, T, work);
+          if (__any_sync(kFullMask, has)) {
+            for (;;) {
+              if (COUNT & K_WIDE) {
+                while (__any_sync(kFullMask, H.node >= 0)) {
+                  if (H.node >= 0) trav_step4<COUNT>(c, H, T, stk);
+#if RT_LEAF_DEFER
+                  flush_leaf<COUNT>(c, H, T);
+#endif
+                }
+              } else {
+                while (__any_sync(kFullMask, H.node >= 0)) {
+                  if (H.node >= 0) trav_step<COUNT, false>(c, H, T, stk);
+                }
+              }
+              unpark(H.node);
+              while (__any_sync(kFullMask, H.node >= 0)) {
+                if (H.node >= 0) trav_step<COUNT, true>(c, H, T, stk);
+              }
+              if (!(COUNT & K_OBJ)) break;
+              if (!__any_sync(kFullMask, next_tree<COUNT>(c, H, T))) break;
+            }
+            if (has) wf_ray_finish(c, w, pcol, kind, H, T);
+          }
+          __syncwarp();
+        }
+        // the path's first lane shades: lighting of the previous hit (shadow results of its lanes), set-up of the new one
+        const bool more = mine && role == 0 && wf_shade<COUNT>(c, w, pcol);
+        __syncwarp();
+        if (!__any_sync(kFullMask, more)) break;
+      }
+    }
   }
 }
 #endif // __CUDACC__

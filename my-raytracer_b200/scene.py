@@ -309,7 +309,7 @@ class DeviceScene:
         """Which pipeline the last frame ran on: "megakernel" (one persistent kernel) or "wavefront"."""
         k = C.c_int()
         check(self.lib.rt_last_pipeline(self.handle, C.byref(k)), self.lib)
-        return "wavefront" if k.value == 1 else "megakernel"
+        return {1: "wavefront", 2: "rayparallel"}.get(k.value, "megakernel")
 
     def last_kernel_ms(self) -> float:
         ms = C.c_float()

@@ -384,3 +384,44 @@ def test_one_sample_per_lane_equals_the_sequential_sample_loop(rt, lib, gpu, nam
         acc = np.where(part != 0.0, part, acc)
     torch.cuda.synchronize()
     assert np.array_equal(acc, whole)
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("rings", dict(width=210, height=150)),                    # deep mirror chains on a PHONG mesh: what the kernel is for
+    ("office", dict(width=322, height=181)),
+    ("spheres", dict(width=128, height=96)),                   # analytic primitives only
+    ("scatter", dict(width=160, height=100, n_objects=20)),    # triangle trees + a tree over analytic spheres (K_OBJ)
+    ("mixed_small", dict(width=161, height=99)),
+])
+def test_ray_parallel_kernel_is_bit_identical_to_the_persistent_kernel(rt, lib, gpu, name, kw):
+    """RT_FLAG_RAY_PARALLEL: the shadow rays and the mirror ray of a hit traced together on neighbouring lanes, the path
+    state in shared memory, the wavefront's stage functions.  Same ids, ray parameters and FP64 pixels as the persistent
+    kernel — with 1, 2-3, 5 and 9 lights (2, 4, 8 lanes per path; more ray kinds than lanes), a 2x2 sample grid and a
+    rank's tile share."""
+    host = rt.HostScene(rt.scenes.REGISTRY[name](**kw), lib)
+    dev = rt.DeviceScene(host)
+    lp0, lc0 = np.asarray(host.lights_pos, np.float64), np.asarray(host.lights_color, np.float64)
+    rng = np.random.default_rng(7)
+
+    def lights(n):
+        if n <= lp0.shape[0]:
+            return lp0[:n].copy(), lc0[:n].copy()
+        extra = n - lp0.shape[0]
+        lp = np.vstack([lp0, np.hstack([rng.uniform(-6, 6, (extra, 2)), rng.uniform(4, 9, (extra, 1)), np.zeros((extra, 1))])])
+        lc = np.vstack([lc0, np.hstack([rng.uniform(0.05, 0.2, (extra, 3)), np.zeros((extra, 1))])])
+        return lp, lc
+
+    for nl, spp, tile in ((lp0.shape[0], 1, (0, 1, 1)), (1, 1, (0, 1, 1)), (5, 1, (0, 1, 1)), (9, 1, (0, 1, 1)),
+                          (lp0.shape[0], 2, (0, 1, 1)), (lp0.shape[0], 1, (1, 3, 2))):
+        lp, lc = lights(nl)
+        want = ("rgba8", "pixels", "hit_id", "hit_t") if spp == 1 else ("rgba8", "pixels")
+        a = dev.render(host.camera, lp, lc, host.params(spp_grid=spp, tile=tile, flags=gpu.RT_FLAG_MEGAKERNEL), want=want)
+        assert dev.last_pipeline() == "megakernel"
+        b = dev.render(host.camera, lp, lc, host.params(spp_grid=spp, tile=tile, flags=gpu.RT_FLAG_RAY_PARALLEL), want=want)
+        assert dev.last_pipeline() == "rayparallel"
+        for k in want:
+            assert np.array_equal(a[k], b[k]), (nl, spp, tile, k)
+        assert a["pixels"][..., :3].max() > 0.0
+    # frames it does not cover fall back to the persistent kernel: instrumented frames, no light at all
+    dev.render(host.camera, lp0, lc0, host.params(flags=gpu.RT_FLAG_RAY_PARALLEL | gpu.RT_FLAG_COUNTERS), want=("rgba8",))
+    assert dev.last_pipeline() == "megakernel"
