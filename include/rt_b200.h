@@ -150,7 +150,10 @@ typedef struct rt_render_params {
                                   lane per light) and its mirror ray are traced together, a path advances one bounce per
                                   round and a warp holds 8 paths instead of 32 pixels.  For frames that are chains of
                                   dependent rays rather than throughput (<= 350 k pixels, deep mirror paths); bit-identical
-                                  pixels.  RT_B200_PIPELINE=rayparallel selects it for every frame it covers. */
+                                  pixels.  Chosen by default for small frames of triangle-mesh scenes with a reflecting material
+                                  (mirror depth >= 2, at most 64 k pixel samples per possible hit of a path, no analytic
+                                  primitives); RT_B200_PIPELINE=rayparallel selects it for every frame it covers,
+                                  RT_B200_PIPELINE=persistent or RT_FLAG_MEGAKERNEL never. */
 #define RT_FLAG_MEGAKERNEL  32 /* always the one persistent kernel (overrides RT_B200_PIPELINE) */
 
 /* Output buffers; any pointer may be NULL.  All are W*H entries, index y*W + x

@@ -75,6 +75,7 @@ struct rt_scene {
   int wavefront_default = 0;             // RT_B200_PIPELINE=wavefront
   int grid_rp[4] = {0, 0, 0, 0};         // the same for rp_render_kernel<cfg> (rays of a path on neighbouring lanes)
   int rp_default = 0;                    // RT_B200_PIPELINE=rayparallel: every frame it covers; -1 (=persistent): never
+  bool has_mirror = false;               // some mesh material reflects (paths can be deep)
   int last_pipeline = 0;                 // what the last launch ran: 0 persistent megakernel, 1 wavefront
   int grid_plain = 0, grid_count = 0;
   int grid_wide = 0, grid_wide_count = 0; // K_WIDE kernels (scenes whose trees all have 4-wide twins)
@@ -212,6 +213,7 @@ int adopt_blob(rt_scene *s) {
   if (h.num_meshes)
     RT_CUDA(cudaMemcpy(meshes.data(), b + h.off_meshes, sizeof(MeshRec) * h.num_meshes, cudaMemcpyDeviceToHost));
   s->tex.assign(h.num_meshes, 0);
+  for (int m = 0; m < h.num_meshes; ++m) s->has_mirror = s->has_mirror || meshes[m].mirror > 0.0;
   for (int m = 0; m < h.num_meshes; ++m) {
     if (meshes[m].tex_w == -1) continue;
     cudaResourceDesc rd;
@@ -337,9 +339,13 @@ int adopt_blob(rt_scene *s) {
   return RT_OK;
 }
 
-constexpr long long kRpAutoPixels = 400000;   // frames up to this many pixel samples default to the ray-parallel kernel
+// Default choice of the ray-parallel kernel: triangle-mesh scenes with a reflecting material, mirror depth >= 2, and at most
+// 64 k pixel samples per possible hit of a path (depth 3: 256 k, depth 5: 384 k).  Measured break-even (profiles/
+// r02_rayparallel_ab2.log): Office (depth 3) wins at 130 k and 230 k pixels and loses at 360 k; rings (depth 5) wins at 88 k
+// and 350 k and loses at 1.4 M; scenes with analytic primitives and scenes without mirrors lose at every size.
+constexpr long long kRpAutoPixelsPerBounce = 65536;
 #ifndef RT_RP_AUTO
-#define RT_RP_AUTO 0
+#define RT_RP_AUTO 1
 #endif
 bool wavefront_ok(const rt_scene *s, const FrameParams &fp, const int *d_list, const int *d_list_count);
 int launch_wavefront(rt_scene *s, const FrameParams &fp, const double *d_lpos, const double *d_lcol, const FrameOut &out,
@@ -393,15 +399,16 @@ int launch(rt_scene *s, const FrameParams &fp, const double *d_lpos, const doubl
     gp = gp < lim ? gp : lim;
   }
   // Small frames are chains of dependent rays, not throughput: the rays of a path on neighbouring lanes (rp_render_kernel,
-  // rt_wavefront.cuh).  Asked for by RT_FLAG_RAY_PARALLEL / RT_B200_PIPELINE=rayparallel, and by default for frames of at
-  // most kRpAutoPixels pixel samples; frames it does not cover (instrumented, pixel lists, dynamic tile queue, no light,
+  // rt_wavefront.cuh).  Asked for by RT_FLAG_RAY_PARALLEL / RT_B200_PIPELINE=rayparallel, and by default for small frames of
+  // mirror scenes (kRpAutoPixelsPerBounce); frames it does not cover (instrumented, pixel lists, dynamic tile queue, no light,
   // more than 30) stay on the persistent kernel, as does everything under RT_FLAG_MEGAKERNEL.
   {
     const long long samples = (long long)fp.cam.width * fp.cam.height * fp.spp_grid * fp.spp_grid;
     const bool covered = !count && !d_list && !d_list_count && fp.num_lights >= 1 && fp.num_lights <= kWfMaxLights &&
                          fp.static_tiles == fp.tiles_x * fp.tiles_y && !(fp.flags & (RT_FLAG_MEGAKERNEL | RT_FLAG_NODES8));
     const bool wanted = (fp.flags & RT_FLAG_RAY_PARALLEL) || s->rp_default > 0 ||
-                        (s->rp_default == 0 && RT_RP_AUTO && samples <= kRpAutoPixels);
+                        (s->rp_default == 0 && RT_RP_AUTO && s->hdr.num_objects == 0 && s->has_mirror && fp.max_depth >= 2 &&
+                         samples <= kRpAutoPixelsPerBounce * (fp.max_depth + 1));
     if (covered && wanted) {
       const bool objt = s->hdr.obj_root >= 0;
       const int cfg = (objt ? 1 : 0) | (wide ? 2 : 0);
