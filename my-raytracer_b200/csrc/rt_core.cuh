@@ -675,13 +675,30 @@ template <int S> RT_HD D3 primary_dir(const Ctx &c, const Cold<S> &C) {
   return sub(add(add(ld3(cam.lower_left), scale(x, ld3(cam.x_dir))), scale(y, ld3(cam.y_dir))), ld3(cam.eye));
 }
 
-template <int COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const Cold<S> &C) {
-  const D3 dir = primary_dir(c, C);
+// A ray the path logic wants traced next.  In the kernels for scenes with analytic primitives advance() collects the
+// request of whichever branch ran and calls start_ray at ONE place: start_ray (normalisation, FP32 ray set-up, the linear
+// list of analytic primitives) is the largest piece of the path logic there.
+struct RayReq {
+  D3 o, d;
+  int mode;
+  double tmax;
+};
+
+template <int COUNT, int S> RT_HD void prep_primary(const Ctx &c, const Cold<S> &C, RayReq &r) {
+  r.o = ld3(c.fp.cam.eye);
+  r.d = primary_dir(c, C);
+  r.mode = M_NEAREST;
+  r.tmax = DBL_MAX;
   C.i(CI_DEPTH) = 0;
   C.d(CD_WEIGHT) = 1.0;
   C.set(CD_COL, mk(0.0, 0.0, 0.0));
   bump<COUNT>(c, C_RAY_PRIMARY);
-  start_ray<COUNT>(c, H, C, ld3(c.fp.cam.eye), dir, M_NEAREST, DBL_MAX);
+}
+
+template <int COUNT, int S> RT_HD void start_primary(const Ctx &c, Hot &H, const Cold<S> &C) {
+  RayReq r;
+  prep_primary<COUNT>(c, C, r);
+  start_ray<COUNT>(c, H, C, r.o, r.d, r.mode, r.tmax);
 }
 
 template <int S> RT_HD void write_pixel(const Ctx &c, const Cold<S> &C) {
@@ -705,22 +722,26 @@ template <int S> RT_HD void write_pixel(const Ctx &c, const Cold<S> &C) {
   }
 }
 
-template <int COUNT, int S> RT_HD void sample_done(const Ctx &c, Hot &H, const Cold<S> &C) {
+// The sample's path has ended.  Returns true (request in r) when the lane goes on with the next sub-pixel sample.
+template <int COUNT, bool DEFER, int S> RT_HD bool sample_done(const Ctx &c, Hot &H, const Cold<S> &C, RayReq &r) {
   if (COUNT & K_SPL) {   // the sample stays in CD_COL until the warp sums the samples of each pixel (rt_kernel.cuh)
     H.mode = M_IDLE;
     H.node = -1;
-    return;
+    return false;
   }
   C.set(CD_ACC, add(C.v(CD_ACC), C.v(CD_COL)));
   const int sample = C.i(CI_SAMPLE) + 1;
   C.i(CI_SAMPLE) = sample;
   if (sample < c.fp.spp_grid * c.fp.spp_grid) {
-    start_primary<COUNT>(c, H, C);
-  } else {
-    write_pixel(c, C);
-    H.mode = M_IDLE;
-    H.node = -1;
+    prep_primary<COUNT>(c, C, r);
+    if (DEFER) return true;
+    start_ray<COUNT>(c, H, C, r.o, r.d, r.mode, r.tmax);
+    return false;
   }
+  write_pixel(c, C);
+  H.mode = M_IDLE;
+  H.node = -1;
+  return false;
 }
 
 // Fill P, N, V, kd, mat for the nearest hit and start the lighting loop (L = ambient term).
@@ -809,10 +830,13 @@ template <int S> RT_HD void add_light(const Ctx &c, const Cold<S> &C, const Mat 
   C.set(CD_L, L);
 }
 
-// Advance a lane whose traversal has finished until it has a new ray in flight or is idle.
-template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<S> &C) {
+// One step of the path logic of a lane whose traversal has finished (H.mode != M_IDLE, H.node == -1).  Returns true
+// when a ray must be started (request in r); false: the lane's state changed, look again.
+// DEFER false: the ray is started right where it is requested (start_ray inlined at every site: straight-line code, the
+// fastest form for the triangle-mesh kernels, profiles/r02_variants.md) and the function returns false.
+template <int COUNT, bool DEFER, int S> RT_HD bool path_step(const Ctx &c, Hot &H, const Cold<S> &C, RayReq &r) {
   const SceneView &sv = c.sv;
-  while (H.mode != M_IDLE && H.node == -1) { // -1: no ray in flight (a parked node is <= -2)
+  {
     Mat m;
     if (H.mode == M_NEAREST) {
       if (C.i(CI_DEPTH) == 0 && c.fp.spp_grid == 1) {
@@ -823,8 +847,7 @@ template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<
       if (H.best_id < 0) {
         // miss: primary -> background; bounce -> weight * background (mytracer_gpu.cu:262,292)
         C.set(CD_COL, add(C.v(CD_COL), scale(C.d(CD_WEIGHT), ld3(c.fp.background))));
-        sample_done<COUNT>(c, H, C);
-        continue;
+        return sample_done<COUNT, DEFER>(c, H, C, r);
       }
       hit_setup<COUNT>(c, H, C, m);
     } else { // M_ANYHIT finished: CI_LIGHT was the light under test
@@ -853,14 +876,15 @@ template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<
           continue;
         }
         if (RT_CACHE_LDIR) C.set(CD_LDIR, ldir);
-        start_ray<COUNT>(c, H, C, add(P, scale(1e-4, ldir)), ldir, M_ANYHIT, ldist);
-        break;
+        C.i(CI_LIGHT) = k;
+        if (!DEFER) { start_ray<COUNT>(c, H, C, add(P, scale(1e-4, ldir)), ldir, M_ANYHIT, ldist); return false; }
+        r.o = add(P, scale(1e-4, ldir)); r.d = ldir; r.mode = M_ANYHIT; r.tmax = ldist;
+        return true;                      // shadow ray of light k
       }
       add_light(c, C, m, k, false);
       ++k;
     }
     C.i(CI_LIGHT) = k;
-    if (H.mode == M_ANYHIT) continue; // shadow ray in flight (or already resolved: node < 0)
     // all lights done: colour of this bounce, then the mirror bounce (mytracer.cpp:546-555)
     const double w = C.d(CD_WEIGHT);
     C.set(CD_COL, add(C.v(CD_COL), scale(w, scale(dsub(1.0, m.mirror), C.v(CD_L)))));
@@ -871,10 +895,23 @@ template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<
       C.d(CD_WEIGHT) = dmul(w, m.mirror);
       C.i(CI_DEPTH) = depth + 1;
       bump<COUNT>(c, C_RAY_REFLECT);
-      start_ray<COUNT>(c, H, C, add(P, scale(1e-4, v)), v, M_NEAREST, DBL_MAX);
-    } else {
-      sample_done<COUNT>(c, H, C);
+      if (!DEFER) { start_ray<COUNT>(c, H, C, add(P, scale(1e-4, v)), v, M_NEAREST, DBL_MAX); return false; }
+      r.o = add(P, scale(1e-4, v)); r.d = v; r.mode = M_NEAREST; r.tmax = DBL_MAX;
+      return true;
     }
+    return sample_done<COUNT, DEFER>(c, H, C, r);
+  }
+}
+
+// Advance a lane whose traversal has finished until it has a new ray in flight or is idle.
+// Kernels whose start_ray is large - a scene with analytic primitives (their linear list is walked at every ray start), and
+// the kernels without 4-wide records (scenes of analytic primitives only, A/B frames) - start rays at ONE place: half the
+// code, 10 % faster on the spheres / molecule frames.  The triangle-mesh kernels keep the inlined copies (3 % faster there).
+template <int COUNT, int S> RT_HD void advance(const Ctx &c, Hot &H, const Cold<S> &C) {
+  constexpr bool kDefer = (COUNT & K_OBJ) != 0 || !(COUNT & K_WIDE);
+  RayReq r;
+  while (H.mode != M_IDLE && H.node == -1) { // -1: no ray in flight (a parked node is <= -2)
+    if (path_step<COUNT, kDefer>(c, H, C, r)) start_ray<COUNT>(c, H, C, r.o, r.d, r.mode, r.tmax);
   }
 }
 
